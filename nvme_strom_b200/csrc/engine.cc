@@ -1,0 +1,266 @@
+/*
+ * engine.cc -- the transfer pipeline: reader threads, pinned double-buffered
+ * staging, cudaMemcpyAsync on per-thread copy streams.
+ *
+ * Stands where the kernel module builds PRP lists and posts NVMe READs whose
+ * DMA lands in GPU BAR1 (kmod/nvme_strom.c:1414-1482 submit_ssd2gpu_memcpy,
+ * :1046-1120 __submit_async_read_cmd, :993-1039 completion callback).  User
+ * space cannot aim the SSD's DMA engine at the GPU without the out-of-tree
+ * module, so each piece goes   file --pread--> pinned slot --H2D--> HBM   and
+ * the pipeline's job is to keep both halves busy at once:
+ *
+ *   - one engine per (device, context); N reader threads each own SLOTS
+ *     pinned staging slots, one CUDA stream and one event per slot;
+ *   - a thread preads piece k+1 into its next slot while the copy of piece k
+ *     is still in flight on its stream (double buffering); it only waits on
+ *     an event when it needs that slot again or runs out of work;
+ *   - completion is a host-side refcount drop (task_put): MEMCPY_WAIT sleeps
+ *     on a futex and never touches CUDA, so it is legal inside a CUDA stream
+ *     callback (utils/nvme_test.c:208-223).
+ *
+ * SSD2RAM pieces have a host destination: pread straight into the caller's
+ * DMA buffer, no staging (kmod/nvme_strom.c:1693-1761).
+ *
+ * Environment: NVME_STROM_READERS (threads per engine, default 12),
+ * NVME_STROM_SLOT_KB (staging slot, default 1024), NVME_STROM_SLOTS (per
+ * thread, default 3), NVME_STROM_HOST_READERS (SSD2RAM threads, default 8).
+ */
+#include "strom_internal.h"
+#include <cstring>
+#include <deque>
+#include <map>
+#include <sched.h>
+#include <thread>
+#include <unistd.h>
+
+namespace strom {
+
+static int env_int(const char *name, int dflt, int lo, int hi)
+{
+	const char *e = getenv(name);
+	int v = e ? atoi(e) : dflt;
+	return v < lo ? lo : (v > hi ? hi : v);
+}
+
+uint32_t engine_piece_max()
+{
+	static uint32_t v = (uint32_t)env_int("NVME_STROM_SLOT_KB", 1024, 128, 65536) << 10;
+	return v;
+}
+
+static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
+{
+	uint32_t done = 0;
+	while (done < len)
+	{
+		ssize_t n = pread(fd, buf + done, len - done, (off_t)(off + done));
+		if (n < 0)
+		{
+			if (errno == EINTR)
+				continue;
+			return -errno;
+		}
+		if (n == 0)
+		{
+			/* past EOF: the module checks only fpos > i_size per chunk (:1529);
+			 * a chunk overlapping EOF reads as zeros beyond it */
+			memset(buf + done, 0, len - done);
+			break;
+		}
+		done += (uint32_t)n;
+	}
+	return 0;
+}
+
+class Engine {
+public:
+	Engine(int device, void *ctx, bool host_only)
+		: device_(device), ctx_(ctx), host_only_(host_only)
+	{
+		int n = host_only ? env_int("NVME_STROM_HOST_READERS", 8, 1, 256)
+						  : env_int("NVME_STROM_READERS", 12, 1, 256);
+		for (int i = 0; i < n; i++)
+			threads_.emplace_back([this, i] { worker(i); });
+	}
+	/* engines live until process exit; threads are detached at teardown */
+	~Engine()
+	{
+		{
+			std::lock_guard<std::mutex> g(lock_);
+			stop_ = true;
+		}
+		cv_.notify_all();
+		for (auto &t : threads_)
+			t.join();
+	}
+	void submit(const std::vector<Job> &jobs)
+	{
+		{
+			std::lock_guard<std::mutex> g(lock_);
+			for (const Job &j : jobs)
+				queue_.push_back(j);
+		}
+		if (jobs.size() > 1)
+			cv_.notify_all();
+		else
+			cv_.notify_one();
+	}
+
+private:
+	struct Slot {
+		char *buf = nullptr;
+		cudaEvent_t ev = nullptr;
+		DmaTask *task = nullptr;          /* non-null while a copy is in flight */
+		uint64_t tsc = 0;
+	};
+
+	bool pop(Job *j, bool block)
+	{
+		std::unique_lock<std::mutex> g(lock_);
+		if (block)
+			cv_.wait(g, [&] { return stop_ || !queue_.empty(); });
+		if (queue_.empty())
+			return false;
+		*j = queue_.front();
+		queue_.pop_front();
+		return true;
+	}
+
+	void retire(Slot &s)
+	{
+		if (!s.task)
+			return;
+		cudaError_t rc = cudaEventSynchronize(s.ev);
+		stats_dma_finished(s.tsc);
+		task_put(s.task, rc == cudaSuccess ? 0 : -EIO);
+		s.task = nullptr;
+	}
+
+	void worker(int index)
+	{
+		(void)index;
+		if (host_only_)
+		{
+			Job j;
+			while (pop(&j, true))
+			{
+				const uint64_t t0 = rdtsc_now();
+				stats_dma_started();
+				int rc = read_fully(j.fd, j.dst, j.length, j.file_off);
+				stats_dma_finished(t0);
+				task_put(j.task, rc);
+			}
+			return;
+		}
+
+		/* GPU engine: bind the context, build the staging ring */
+		const DriverApi &api = driver_api();
+		const bool bound = (ctx_ && api.ok && api.cuCtxSetCurrent(ctx_) == 0) ||
+					   cudaSetDevice(device_) == cudaSuccess;
+		const int n_slots = env_int("NVME_STROM_SLOTS", 3, 2, 16);
+		const uint32_t slot_sz = engine_piece_max();
+		std::vector<Slot> slots((size_t)n_slots);
+		cudaStream_t stream = nullptr;
+		bool ready = bound && cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking) == cudaSuccess;
+		for (int i = 0; ready && i < n_slots; i++)
+		{
+			if (cudaHostAlloc((void **)&slots[i].buf, slot_sz, cudaHostAllocPortable) != cudaSuccess ||
+				cudaEventCreateWithFlags(&slots[i].ev, cudaEventDisableTiming) != cudaSuccess)
+				ready = false;
+		}
+		if (!ready)
+		{
+			(void)cudaGetLastError();
+			logf(0, "engine(dev=%d): cannot set up staging; failing its jobs", device_);
+		}
+
+		int next = 0;
+		Job j;
+		for (;;)
+		{
+			/* nothing queued: finish what is in flight before sleeping */
+			if (!pop(&j, false))
+			{
+				for (Slot &s : slots)
+					retire(s);
+				if (!pop(&j, true))
+					break;
+			}
+			if (!ready)
+			{
+				task_put(j.task, -EIO);
+				continue;
+			}
+			Slot &s = slots[(size_t)next];
+			next = (next + 1) % n_slots;
+			retire(s);                            /* slot's previous copy must be done */
+			const uint64_t t0 = rdtsc_now();
+			int rc = read_fully(j.fd, s.buf, j.length, j.file_off);
+			if (rc == 0)
+			{
+				stats_dma_started();
+				cudaError_t cr = cudaMemcpyAsync(j.dst, s.buf, j.length, cudaMemcpyHostToDevice, stream);
+				if (cr == cudaSuccess)
+					cr = cudaEventRecord(s.ev, stream);
+				if (cr != cudaSuccess)
+				{
+					(void)cudaGetLastError();
+					stats_dma_finished(t0);
+					rc = -EIO;
+				}
+			}
+			if (stat_info_level() > 0)
+			{
+				const uint64_t t1 = rdtsc_now();
+				g_stats.nr_submit_dma++;
+				g_stats.clk_submit_dma += t1 > t0 ? t1 - t0 : 0;
+			}
+			if (rc != 0)
+				task_put(j.task, rc);
+			else
+			{
+				s.task = j.task;
+				s.tsc = t0;
+			}
+		}
+		for (Slot &s : slots)
+			retire(s);
+	}
+
+	int device_;
+	void *ctx_;
+	bool host_only_;
+	std::mutex lock_;
+	std::condition_variable cv_;
+	std::deque<Job> queue_;
+	bool stop_ = false;
+	std::vector<std::thread> threads_;
+};
+
+static std::mutex g_engine_lock;
+static std::map<std::pair<int, void *>, Engine *> g_engines;
+static Engine *g_host_engine;
+
+Engine *engine_for_window(const GpuWindow &w)
+{
+	std::lock_guard<std::mutex> g(g_engine_lock);
+	auto key = std::make_pair(w.device, w.ctx);
+	auto it = g_engines.find(key);
+	if (it != g_engines.end())
+		return it->second;
+	Engine *e = new Engine(w.device, w.ctx, false);
+	g_engines[key] = e;
+	return e;
+}
+
+Engine *engine_for_host()
+{
+	std::lock_guard<std::mutex> g(g_engine_lock);
+	if (!g_host_engine)
+		g_host_engine = new Engine(-1, nullptr, true);
+	return g_host_engine;
+}
+
+void engine_submit(Engine *e, const std::vector<Job> &jobs) { e->submit(jobs); }
+
+} /* namespace strom */

@@ -1,0 +1,477 @@
+/*
+ * page_scan.cu -- sm_100a kernels over landed 8KB PostgreSQL heap pages:
+ * pg_checksum_page + PageIsVerified header test + line-pointer validation in
+ * ONE pass over the bytes, optionally fused with the byte-compare against a
+ * second copy of the pages.
+ *
+ * Takes over: the line-pointer walk of pgsql/nvme_strom.c:1069-1081 /
+ * :909-937, PostgreSQL's checksum (un-vendored dependency of the reference),
+ * and -- in the fused form -- the memcmp of utils/nvme_test.c:254-266.
+ *
+ * A page is uint32 data[64][32].  Column j of every 128-byte row feeds FNV
+ * stream j: 32 independent chains of 64 dependent steps, so the work maps to
+ * "one thread owns some columns for all 64 rows".  HBM-bound (8192 B read,
+ * 8 B written per page; ~0.5 integer ops per byte), no tensor-core shape.
+ * Two kernels, same arithmetic (page_math.cuh):
+ *
+ *  scan_tma_kernel<W,S>   one warp per page, lane j = column j.  Each warp
+ *      owns a private ring of S 8KB shared-memory slots filled by 1-D bulk
+ *      async copies (cp.async.bulk -> UBLKCP) that complete on an mbarrier;
+ *      lane 0 re-arms a slot as soon as the warp has read it.  Up to
+ *      W*S*8KB (192KB) in flight per SM without holding registers.
+ *  scan_ldg_kernel<R,V>   8 lanes per page, each lane owns 4 columns and
+ *      streams its 16-byte slice of every row with ld.global.nc.v4, R rows
+ *      ahead (double-buffered in registers).  V fuses the compare.
+ */
+#include "common.h"
+#include "page_math.cuh"
+#include <cstdlib>
+#include <cstring>
+
+namespace strom {
+
+struct ScanArgs {
+	const uint4 *pages;
+	const uint4 *ref;            /* fused compare only */
+	uint64_t n_pages;
+	uint64_t base_offset;        /* added to FIRST_MISMATCH */
+	uint32_t first_blkno;
+	StromPageResult *results;    /* may be null */
+	unsigned long long *totals;
+};
+
+/* ------------------------------------------------------------------ */
+/* mbarrier / bulk-copy primitives (PTX; SASS: SYNCS.*, UBLKCP)        */
+/* ------------------------------------------------------------------ */
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+	return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+				 :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+	uint32_t done;
+	do {
+		asm volatile("{\n\t.reg .pred p;\n\t"
+					 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+					 "selp.u32 %0, 1, 0, p;\n\t}"
+					 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+	} while (!done);
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+				 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+/* ------------------------------------------------------------------ */
+/* kernel 1: bulk-copy ring, one warp per page                         */
+/* ------------------------------------------------------------------ */
+template <int W, int S>
+__global__ void __launch_bounds__(W * 32, 1)
+scan_tma_kernel(ScanArgs a)
+{
+	extern __shared__ __align__(128) unsigned char smem[];
+	__shared__ unsigned long long s_tot[STROM_T_COUNT];
+	__shared__ __align__(8) unsigned long long s_bar[W * S];
+
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint64_t stride = (uint64_t)gridDim.x * W;
+	uint64_t page = (uint64_t)blockIdx.x * W + warp;
+	unsigned char *ring = smem + (size_t)warp * S * STROM_BLCKSZ;
+	const uint32_t ring_u32 = smem_u32(ring);
+	const uint32_t bar0 = smem_u32(&s_bar[warp * S]);
+	const unsigned char *gsrc = reinterpret_cast<const unsigned char *>(a.pages);
+	const uint32_t seed = kLaneSeed[lane];
+	TotalsAcc acc;
+
+	if (lane == 0)
+	{
+#pragma unroll
+		for (int s = 0; s < S; s++)
+			mbar_init(bar0 + 8 * s, 1);
+		mbar_fence_init();
+		/* prologue: fill the ring */
+		uint64_t p = page;
+#pragma unroll
+		for (int s = 0; s < S; s++, p += stride)
+			if (p < a.n_pages)
+			{
+				mbar_expect_tx(bar0 + 8 * s, STROM_BLCKSZ);
+				bulk_g2s(ring_u32 + s * STROM_BLCKSZ, gsrc + p * STROM_BLCKSZ, STROM_BLCKSZ, bar0 + 8 * s);
+			}
+	}
+	__syncwarp();
+
+	uint32_t phases = 0;
+	int s = 0;
+	for (; page < a.n_pages; page += stride)
+	{
+		mbar_wait(bar0 + 8 * s, (phases >> s) & 1u);
+		phases ^= (1u << s);
+
+		const uint32_t *pw = reinterpret_cast<const uint32_t *>(ring + (size_t)s * STROM_BLCKSZ);
+		const PageHeader h = decode_header(pw[2], pw[3], pw[4]);      /* broadcast reads */
+		const uint32_t lp_end = kHdrWords + h.nlp;
+		uint32_t sum = seed, orv = 0, cnt = 0;
+
+#pragma unroll
+		for (int b = 0; b < 4; b++)
+		{
+			uint32_t v[16];
+#pragma unroll
+			for (int r = 0; r < 16; r++)
+				v[r] = pw[(b * 16 + r) * 32 + lane];                   /* conflict-free */
+#pragma unroll
+			for (int r = 0; r < 16; r++)
+			{
+				const uint32_t row = b * 16 + r;
+				uint32_t w = v[r];
+				orv |= w;
+				if (row * 32 < lp_end)                                 /* warp-uniform */
+				{
+					const uint32_t widx = row * 32 + lane;
+					if (widx >= kHdrWords && widx < lp_end)
+						cnt += lp_check(w, h);
+				}
+				if (row == 0 && lane == 2)
+					w &= 0xFFFF0000u;                                  /* pd_checksum := 0 */
+				sum = fnv_mix(sum, w);
+			}
+		}
+		__syncwarp();
+		/* every lane has its words in registers: hand the slot back */
+		const uint64_t refill = page + (uint64_t)S * stride;
+		if (lane == 0 && refill < a.n_pages)
+		{
+			mbar_expect_tx(bar0 + 8 * s, STROM_BLCKSZ);
+			bulk_g2s(ring_u32 + s * STROM_BLCKSZ, gsrc + refill * STROM_BLCKSZ, STROM_BLCKSZ, bar0 + 8 * s);
+		}
+		sum = fnv_mix(fnv_mix(sum, 0), 0);
+		const uint32_t hash = __reduce_xor_sync(0xFFFFFFFFu, sum);
+		const uint32_t any = __reduce_or_sync(0xFFFFFFFFu, orv);
+		cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
+		if (lane == 0)
+		{
+			StromPageResult r = finish_page(hash, a.first_blkno + (uint32_t)page, any == 0, h, cnt);
+			if (a.results)
+				a.results[page] = r;
+			acc.add(r);
+		}
+		s = (s + 1 == S) ? 0 : s + 1;
+	}
+	flush_totals(acc, lane == 0, s_tot, a.totals);
+}
+
+/* ------------------------------------------------------------------ */
+/* kernel 2: register streaming, 8 lanes per page                      */
+/* ------------------------------------------------------------------ */
+constexpr int kLdgThreads = 256;
+
+template <int R, bool VERIFY, int MINB>
+__global__ void __launch_bounds__(kLdgThreads, MINB)
+scan_ldg_kernel(ScanArgs a)
+{
+	__shared__ unsigned long long s_tot[STROM_T_COUNT];
+	constexpr int NB = 64 / R;
+	constexpr uint32_t FULL = 0xFFFFFFFFu;
+	const uint32_t lane = threadIdx.x & 31, k = lane & 7, gbase = lane & ~7u;
+	const uint64_t n_groups = ((uint64_t)gridDim.x * blockDim.x) >> 3;
+	uint64_t page = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+	uint64_t wpage = page - (lane >> 3);                 /* page of the warp's group 0 */
+	const uint32_t seed0 = kLaneSeed[4 * k], seed1 = kLaneSeed[4 * k + 1],
+				   seed2 = kLaneSeed[4 * k + 2], seed3 = kLaneSeed[4 * k + 3];
+	TotalsAcc acc;
+
+	if (wpage < a.n_pages)
+	{
+		/* groups past the end shadow the last page and keep quiet, so that
+		 * the warp-wide shuffles below always see all 32 lanes */
+		bool valid = page < a.n_pages;
+		const uint4 *p = a.pages + (valid ? page : a.n_pages - 1) * 512 + k;
+		const uint4 *q = VERIFY ? a.ref + (valid ? page : a.n_pages - 1) * 512 + k : nullptr;
+		uint4 cur[R], nxt[R], rcur[VERIFY ? R : 1], rnxt[VERIFY ? R : 1];
+
+#pragma unroll
+		for (int r = 0; r < R; r++)
+		{
+			cur[r] = ldg_stream(p + r * 8);
+			if (VERIFY) rcur[r] = ldg_stream(q + r * 8);
+		}
+		for (;;)
+		{
+			const uint64_t npage = page + n_groups, nwpage = wpage + n_groups;
+			const bool nvalid = npage < a.n_pages, more = nwpage < a.n_pages;
+			const uint4 *np = a.pages + (nvalid ? npage : a.n_pages - 1) * 512 + k;
+			const uint4 *nq = VERIFY ? a.ref + (nvalid ? npage : a.n_pages - 1) * 512 + k : nullptr;
+			uint32_t s0 = seed0, s1 = seed1, s2 = seed2, s3 = seed3;
+			uint32_t orv = 0, cnt = 0, first_unit = 0xFFFFu;
+			PageHeader h;
+			uint32_t lp_end = 0;
+
+#pragma unroll
+			for (int b = 0; b < NB; b++)
+			{
+				if (b + 1 < NB)
+				{
+#pragma unroll
+					for (int r = 0; r < R; r++)
+					{
+						nxt[r] = ldg_stream(p + ((b + 1) * R + r) * 8);
+						if (VERIFY) rnxt[r] = ldg_stream(q + ((b + 1) * R + r) * 8);
+					}
+				}
+				else if (more)
+				{
+#pragma unroll
+					for (int r = 0; r < R; r++)
+					{
+						nxt[r] = ldg_stream(np + r * 8);
+						if (VERIFY) rnxt[r] = ldg_stream(nq + r * 8);
+					}
+				}
+				if (b == 0)
+				{
+					const uint32_t w2 = __shfl_sync(FULL, cur[0].z, gbase);
+					const uint32_t w3 = __shfl_sync(FULL, cur[0].w, gbase);
+					const uint32_t w4 = __shfl_sync(FULL, cur[0].x, gbase + 1);
+					h = decode_header(w2, w3, w4);
+					lp_end = kHdrWords + h.nlp;
+				}
+#pragma unroll
+				for (int r = 0; r < R; r++)
+				{
+					const uint32_t row = b * R + r;
+					uint4 v = cur[r];
+					orv |= v.x | v.y | v.z | v.w;
+					if (VERIFY)
+					{
+						const uint4 u = rcur[r];
+						if (((v.x ^ u.x) | (v.y ^ u.y) | (v.z ^ u.z) | (v.w ^ u.w)) != 0)
+							first_unit = min(first_unit, row * 8 + k);
+					}
+					if (row * 32 < lp_end)
+					{
+						const uint32_t widx = row * 32 + 4 * k;
+						if (widx + 0 >= kHdrWords && widx + 0 < lp_end) cnt += lp_check(v.x, h);
+						if (widx + 1 >= kHdrWords && widx + 1 < lp_end) cnt += lp_check(v.y, h);
+						if (widx + 2 >= kHdrWords && widx + 2 < lp_end) cnt += lp_check(v.z, h);
+						if (widx + 3 >= kHdrWords && widx + 3 < lp_end) cnt += lp_check(v.w, h);
+					}
+					if (row == 0 && k == 0)
+						v.z &= 0xFFFF0000u;                            /* pd_checksum := 0 */
+					s0 = fnv_mix(s0, v.x);
+					s1 = fnv_mix(s1, v.y);
+					s2 = fnv_mix(s2, v.z);
+					s3 = fnv_mix(s3, v.w);
+				}
+#pragma unroll
+				for (int r = 0; r < R; r++)
+				{
+					cur[r] = nxt[r];
+					if (VERIFY) rcur[r] = rnxt[r];
+				}
+			}
+			uint32_t hash = fnv_mix(fnv_mix(s0, 0), 0) ^ fnv_mix(fnv_mix(s1, 0), 0) ^
+							fnv_mix(fnv_mix(s2, 0), 0) ^ fnv_mix(fnv_mix(s3, 0), 0);
+#pragma unroll
+			for (int d = 4; d >= 1; d >>= 1)
+			{
+				hash ^= __shfl_xor_sync(FULL, hash, d);
+				orv |= __shfl_xor_sync(FULL, orv, d);
+				cnt += __shfl_xor_sync(FULL, cnt, d);
+				if (VERIFY) first_unit = min(first_unit, __shfl_xor_sync(FULL, first_unit, d));
+			}
+			if (k == 0 && valid)
+			{
+				StromPageResult r = finish_page(hash, a.first_blkno + (uint32_t)page, orv == 0, h, cnt);
+				if (a.results)
+					a.results[page] = r;
+				acc.add(r);
+				if (VERIFY && first_unit != 0xFFFFu)
+				{
+					acc.mismatch++;
+					acc.first = min(acc.first, (unsigned long long)(a.base_offset + page * STROM_BLCKSZ + first_unit * 16));
+				}
+			}
+			if (!more)
+				break;
+			page = npage; wpage = nwpage; valid = nvalid; p = np; q = nq;
+		}
+	}
+	flush_totals(acc, k == 0, s_tot, a.totals);
+}
+
+__global__ void totals_reset_kernel(unsigned long long *t)
+{
+	if (threadIdx.x < STROM_T_COUNT)
+		t[threadIdx.x] = (threadIdx.x == STROM_T_FIRST_MISMATCH) ? ~0ull : 0ull;
+}
+
+/* ------------------------------------------------------------------ */
+/* launch plumbing                                                     */
+/* ------------------------------------------------------------------ */
+struct DeviceInfo { int sm_count = 0; bool attr_set[16] = {}; };
+static DeviceInfo g_dev[64];
+
+static DeviceInfo *device_info()
+{
+	int dev = 0;
+	if (cuda_failed(cudaGetDevice(&dev), "cudaGetDevice") || dev < 0 || dev >= 64)
+		return nullptr;
+	DeviceInfo *d = &g_dev[dev];
+	if (d->sm_count == 0)
+	{
+		int n = 0;
+		if (cuda_failed(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev),
+						"cudaDeviceGetAttribute"))
+			return nullptr;
+		d->sm_count = n;
+	}
+	return d;
+}
+
+/* NVME_STROM_SCAN_VARIANT = "tma:W:S" (warps, slots per warp) | "ldg:R:B" (rows
+ * in flight, min blocks per SM); default picked by measurement */
+struct Variant { bool tma; int a, b; };
+static Variant pick_variant(uint32_t flags)
+{
+	Variant v = {true, 8, 3};
+	const char *e = getenv("NVME_STROM_SCAN_VARIANT");
+	if (e && !strncmp(e, "tma:", 4)) { v.tma = true; sscanf(e + 4, "%d:%d", &v.a, &v.b); }
+	else if (e && !strncmp(e, "ldg:", 4)) { v.tma = false; v.a = 8; v.b = 2; sscanf(e + 4, "%d:%d", &v.a, &v.b); }
+	if (flags & STROM_SCAN_KERNEL_LDG) { if (v.tma) { v.tma = false; v.a = 8; v.b = 2; } }
+	if (flags & STROM_SCAN_KERNEL_TMA) { if (!v.tma) { v.tma = true; v.a = 8; v.b = 3; } }
+	return v;
+}
+
+template <int W, int S>
+static int launch_tma(DeviceInfo *d, int slot, const ScanArgs &a, cudaStream_t st)
+{
+	const size_t smem = (size_t)W * S * STROM_BLCKSZ;
+	if (!d->attr_set[slot])
+	{
+		STROM_CUDA_OR_FAIL(cudaFuncSetAttribute(scan_tma_kernel<W, S>,
+												cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		d->attr_set[slot] = true;
+	}
+	uint64_t want = (a.n_pages + W - 1) / W;
+	int grid = (int)(want < (uint64_t)d->sm_count ? want : (uint64_t)d->sm_count);
+	scan_tma_kernel<W, S><<<grid, W * 32, smem, st>>>(a);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	return 0;
+}
+
+template <int R, bool V, int MINB>
+static int launch_ldg(DeviceInfo *d, int slot, const ScanArgs &a, cudaStream_t st)
+{
+	static int occ[64][16];
+	int dev = (int)(d - g_dev);
+	if (occ[dev][slot] == 0)
+	{
+		int n = 0;
+		STROM_CUDA_OR_FAIL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_ldg_kernel<R, V, MINB>,
+																		 kLdgThreads, 0));
+		occ[dev][slot] = n > 0 ? n : 1;
+	}
+	uint64_t want = (a.n_pages * 8 + kLdgThreads - 1) / kLdgThreads;
+	uint64_t cap = (uint64_t)d->sm_count * occ[dev][slot];
+	int grid = (int)(want < cap ? want : cap);
+	scan_ldg_kernel<R, V, MINB><<<grid, kLdgThreads, 0, st>>>(a);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	return 0;
+}
+
+static int check_args(const void *pages, const void *ref, bool need_ref, StromScanTotals *tot)
+{
+	if (!pages || !tot || (need_ref && !ref) ||
+		((uintptr_t)pages & 15) || ((uintptr_t)ref & 15) || ((uintptr_t)tot & 7))
+	{
+		set_error("scan: null or misaligned pointer");
+		errno = EINVAL;
+		return -1;
+	}
+	return 0;
+}
+
+} /* namespace strom */
+
+using namespace strom;
+
+extern "C" int strom_totals_reset_dev(StromScanTotals *d_totals, void *stream)
+{
+	if (!d_totals) { errno = EINVAL; return -1; }
+	totals_reset_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((unsigned long long *)d_totals);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	return 0;
+}
+
+extern "C" int strom_scan_pages_dev(const void *d_pages, uint64_t n_pages, uint32_t first_blkno,
+									uint32_t flags, StromPageResult *d_results,
+									StromScanTotals *d_totals, void *stream)
+{
+	if (check_args(d_pages, nullptr, false, d_totals))
+		return -1;
+	if (n_pages == 0)
+		return 0;
+	DeviceInfo *d = device_info();
+	if (!d) return -1;
+	ScanArgs a = {(const uint4 *)d_pages, nullptr, n_pages, 0, first_blkno, d_results,
+				  (unsigned long long *)d_totals};
+	cudaStream_t st = (cudaStream_t)stream;
+	Variant v = pick_variant(flags);
+	if (v.tma)
+	{
+		if (v.a == 4 && v.b == 6)  return launch_tma<4, 6>(d, 0, a, st);
+		if (v.a == 6 && v.b == 4)  return launch_tma<6, 4>(d, 1, a, st);
+		if (v.a == 12 && v.b == 2) return launch_tma<12, 2>(d, 2, a, st);
+		if (v.a == 7 && v.b == 4)  return launch_tma<7, 4>(d, 3, a, st);
+		if (v.a == 16 && v.b == 1) return launch_tma<16, 1>(d, 4, a, st);
+		if (v.a == 8 && v.b == 2)  return launch_tma<8, 2>(d, 5, a, st);
+		if (v.a == 14 && v.b == 2) return launch_tma<14, 2>(d, 6, a, st);
+		return launch_tma<8, 3>(d, 7, a, st);
+	}
+	if (v.a == 4 && v.b == 1)  return launch_ldg<4, false, 1>(d, 8, a, st);
+	if (v.a == 8 && v.b == 1)  return launch_ldg<8, false, 1>(d, 9, a, st);
+	if (v.a == 4 && v.b == 3)  return launch_ldg<4, false, 3>(d, 10, a, st);
+	if (v.a == 4)  return launch_ldg<4, false, 2>(d, 11, a, st);
+	return launch_ldg<8, false, 2>(d, 12, a, st);
+}
+
+extern "C" int strom_scan_verify_pages_dev(const void *d_pages, const void *d_ref, uint64_t n_pages,
+										   uint32_t first_blkno, uint32_t flags, uint64_t base_offset,
+										   StromPageResult *d_results, StromScanTotals *d_totals,
+										   void *stream)
+{
+	(void)flags;
+	if (check_args(d_pages, d_ref, true, d_totals))
+		return -1;
+	if (n_pages == 0)
+		return 0;
+	DeviceInfo *d = device_info();
+	if (!d) return -1;
+	ScanArgs a = {(const uint4 *)d_pages, (const uint4 *)d_ref, n_pages, base_offset, first_blkno,
+				  d_results, (unsigned long long *)d_totals};
+	const char *e = getenv("NVME_STROM_FUSED_R");
+	if (e && atoi(e) == 41)
+		return launch_ldg<4, true, 1>(d, 13, a, (cudaStream_t)stream);
+	if (e && atoi(e) == 2)
+		return launch_ldg<2, true, 2>(d, 14, a, (cudaStream_t)stream);
+	return launch_ldg<4, true, 2>(d, 15, a, (cudaStream_t)stream);
+}

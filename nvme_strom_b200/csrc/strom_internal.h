@@ -1,0 +1,154 @@
+/*
+ * strom_internal.h -- host-side objects of libnvme_strom.
+ *
+ * The reference keeps these inside the kernel module; here they are plain
+ * user-space tables:
+ *   GpuWindow   <- mapped_gpu_memory        (kmod/pmemmap.c:33-73)
+ *   DmaBuffer   <- strom_dma_buffer         (kmod/pmemmap.c:506-515)
+ *   DmaTask     <- strom_dma_task           (kmod/nvme_strom.c:512-553)
+ *   Plan/Piece  <- the pending request that memcpy_from_nvme_ssd merges into
+ *                  and submit_*_memcpy turns into one NVMe READ
+ *                  (kmod/nvme_strom.c:1302-1405, :1414-1482)
+ *   Engine      <- the NVMe submission queue + PRP pool (:833-1120): reader
+ *                  threads, pinned double-buffered staging, copy streams
+ */
+#pragma once
+#include "common.h"
+#include "nvme_strom.h"
+#include <atomic>
+#include <condition_variable>
+#include <memory>
+#include <mutex>
+#include <vector>
+
+namespace strom {
+
+constexpr uint32_t kGpuBoundShift = 16;                 /* 64KB, pmemmap.c:28       */
+constexpr uint64_t kGpuBoundSize = 1ull << kGpuBoundShift;
+constexpr uint32_t kPageSz = 4096;                       /* PAGE_CACHE_SIZE           */
+constexpr uint32_t kSectorSz = 512;
+constexpr uint32_t kDmaReqMax = 128u << 10;              /* NVMESSD_DMAREQ_MAXSZ :125 */
+constexpr int      kEnotsupp = 524;                      /* kernel-internal ENOTSUPP  */
+
+/* ---- registered device memory ------------------------------------------ */
+struct GpuWindow {
+	unsigned long handle = 0;
+	int           device = -1;
+	void         *ctx = nullptr;          /* CUcontext that owns the allocation */
+	uint64_t      vaddress = 0;           /* as given by the caller             */
+	uint64_t      map_address = 0;        /* vaddress rounded down to 64KB      */
+	uint64_t      map_offset = 0;         /* vaddress & 0xFFFF                  */
+	uint64_t      map_length = 0;         /* map_offset + length                */
+	uint32_t      owner = 0;              /* effective uid                      */
+	uint32_t      version = 1;
+	std::atomic<int> inflight{0};         /* tasks landing here                 */
+};
+std::shared_ptr<GpuWindow> window_get(unsigned long handle);     /* ENOENT rules applied */
+void window_release(const std::shared_ptr<GpuWindow> &w);        /* one task done        */
+
+int do_map_gpu_memory(StromCmd__MapGpuMemory *arg);
+int do_unmap_gpu_memory(StromCmd__UnmapGpuMemory *arg);
+int do_list_gpu_memory(StromCmd__ListGpuMemory *arg);
+int do_info_gpu_memory(StromCmd__InfoGpuMemory *arg);
+
+/* make the window's device/context current on the calling thread */
+int window_make_current(const GpuWindow &w);
+
+/* ---- host DMA buffers ---------------------------------------------------- */
+int do_alloc_dma_buffer(StromCmd__AllocDMABuffer *arg);
+/* resolves a user address to (offset inside the buffer, bytes left in the
+ * mapping).  -EINVAL if the address is not in a mapping of one of our
+ * buffers. */
+int dmabuf_resolve(const void *uaddr, uint64_t *buf_offset, uint64_t *bytes_left,
+				   uint64_t *buf_length);
+
+/* ---- asynchronous tasks --------------------------------------------------- */
+struct DmaTask {
+	unsigned long id = 0;
+	int           session = 0;
+	int           fd = -1;                /* our own dup of the caller's fd     */
+	int           fd_direct = -1;         /* O_DIRECT reopen, or -1             */
+	std::atomic<int>  pending{1};         /* 1 (creator) + pieces in flight     */
+	std::atomic<long> status{0};          /* first error wins, :680-686         */
+	std::shared_ptr<GpuWindow> window;    /* null for SSD2RAM                   */
+	uint64_t      tsc_start = 0;
+};
+DmaTask *task_create(int session, int fd, std::shared_ptr<GpuWindow> win);
+void task_add_ref(DmaTask *t, int n);
+void task_put(DmaTask *t, long status);   /* may free t                          */
+int  task_wait(unsigned long id, long *status, bool interruptible);
+void task_session_closed(int session);
+
+/* ---- planner ---------------------------------------------------------------- */
+struct Piece {                            /* one pread + one copy                */
+	uint64_t file_off;
+	uint64_t dest_off;                    /* bytes from window start / host base */
+	uint32_t length;
+};
+struct Plan {
+	uint32_t nr_cached = 0, nr_direct = 0, nr_dma_submit = 0, nr_dma_blocks = 0;
+	std::vector<uint32_t> ids_out;        /* ssd2gpu: landed order               */
+	std::vector<Piece> pieces;            /* transfer pieces, <= piece_max each  */
+	std::vector<std::pair<uint64_t, uint32_t>> cached;  /* (file_off, slot index) */
+};
+struct FileExtent { uint64_t logical, physical, length; };
+struct FileInfo {
+	uint64_t size = 0;
+	bool     have_extents = false;
+	std::vector<FileExtent> extents;      /* FIEMAP, sorted by logical           */
+};
+struct PlanInput {
+	bool        to_gpu;
+	uint32_t    nr_chunks, chunk_sz, relseg_sz;
+	const uint32_t *chunk_ids;
+	uint64_t    dest_offset, dest_length, dest_segment_sz;
+	const FileInfo *file;
+	const uint8_t *page_state;            /* per 4KB file page, may be null      */
+	uint64_t    n_state_pages;
+	uint32_t    piece_max;                /* staging slot size                   */
+};
+int plan_chunks(const PlanInput &in, Plan *out);          /* 0 or -errno         */
+int file_info_get(int fd, FileInfo *info, bool want_extents);
+/* residency of the 4KB pages of [off, off+len) via mincore on a transient map */
+int file_page_state(int fd, uint64_t off, uint64_t len, std::vector<uint8_t> *state);
+
+/* ---- engines ------------------------------------------------------------------ */
+struct Job {
+	DmaTask *task;
+	int      fd;
+	bool     direct;
+	uint64_t file_off;
+	uint32_t length;
+	char    *dst;                         /* device or host address              */
+};
+class Engine;
+Engine *engine_for_window(const GpuWindow &w);            /* created on demand   */
+Engine *engine_for_host();
+void engine_submit(Engine *e, const std::vector<Job> &jobs);
+uint32_t engine_piece_max();                              /* staging slot size   */
+
+/* ---- statistics (kmod/nvme_strom.c:64-86) --------------------------------------- */
+struct Stats {
+	std::atomic<uint64_t> nr_ssd2gpu{0}, clk_ssd2gpu{0}, nr_setup_prps{0}, clk_setup_prps{0},
+		nr_submit_dma{0}, clk_submit_dma{0}, nr_wait_dtask{0}, clk_wait_dtask{0},
+		nr_wrong_wakeup{0}, cur_dma_count{0}, max_dma_count{0},
+		nr_debug1{0}, clk_debug1{0}, nr_debug2{0}, clk_debug2{0},
+		nr_debug3{0}, clk_debug3{0}, nr_debug4{0}, clk_debug4{0};
+};
+extern Stats g_stats;
+int stat_info_level();                    /* NVME_STROM_STAT_INFO, default 1     */
+void stats_dma_started();
+void stats_dma_finished(uint64_t tsc_start);
+
+/* driver-API entry points fetched through the runtime (no link to libcuda) */
+struct DriverApi {
+	int (*cuPointerGetAttribute)(void *data, int attr, unsigned long long ptr) = nullptr;
+	int (*cuCtxSetCurrent)(void *ctx) = nullptr;
+	int (*cuCtxGetCurrent)(void **ctx) = nullptr;
+	int (*cuMemGetAddressRange)(unsigned long long *base, size_t *size, unsigned long long ptr) = nullptr;
+	int (*cuDevicePrimaryCtxRetain)(void **ctx, int dev) = nullptr;
+	bool ok = false;
+};
+const DriverApi &driver_api();
+
+} /* namespace strom */

@@ -1,0 +1,194 @@
+"""Host-side driver of the segment pipeline, the Python twin of the reference's
+``exec_test_by_strom`` (utils/nvme_test.c:382-498, slots set up at :276-323).
+
+Per segment: fill ``chunk_ids`` (:432-433) -> ``MEMCPY_SSD2GPU`` (:435) ->
+``MEMCPY_WAIT`` (:208-223).  Where the reference then copies the segment back
+and memcmp's it on the CPU (:462-469, :225-274), this driver leaves the bytes
+in HBM and launches the page kernels on them; only the counters come back.
+
+torch is used for device memory, streams and events only.  Every operation on
+the data goes through the C ABI of libnvme_strom.
+"""
+import ctypes as C
+import os
+from collections import deque
+
+import numpy as np
+import torch
+
+from . import abi
+from .abi import lib
+
+BLCKSZ = abi.BLCKSZ
+
+
+class _Slot:
+    __slots__ = ("index", "offset", "chunk_ids", "uarg", "event", "busy", "first_page", "ref_host",
+                 "ref_dev", "wb")
+
+
+class SegmentPipeline:
+    """N in-flight segments of ``segment_sz`` bytes landing in one mapped device buffer."""
+
+    def __init__(self, device=0, segment_sz=32 << 20, nr_segments=6, verify=False, scan=True,
+                 scan_flags=abi.SCAN_DEFAULT, keep_results=False):
+        if segment_sz % BLCKSZ:
+            raise ValueError("segment size must be a multiple of 8192")
+        self.device = torch.device("cuda", device)
+        torch.cuda.set_device(self.device)
+        self.segment_sz = segment_sz
+        self.nr_segments = nr_segments
+        self.nr_chunks = segment_sz // BLCKSZ
+        self.verify = verify
+        self.scan = scan
+        self.scan_flags = scan_flags
+        self.keep_results = keep_results
+        self.stream = torch.cuda.Stream(device=self.device)
+        self.buffer = torch.empty(segment_sz * nr_segments, dtype=torch.uint8, device=self.device)
+        self.totals = torch.zeros(abi.T_COUNT, dtype=torch.int64, device=self.device)
+        self.results = None
+        marg = abi.StromCmd__MapGpuMemory()
+        marg.vaddress = self.buffer.data_ptr()
+        marg.length = self.buffer.numel()
+        abi.nvme_strom_ioctl(abi.STROM_IOCTL__MAP_GPU_MEMORY, marg)
+        self.handle = marg.handle
+        self.h2d_bytes = 0
+        self.slots = []
+        for i in range(nr_segments):
+            s = _Slot()
+            s.index = i
+            s.offset = i * segment_sz
+            s.chunk_ids = (C.c_uint32 * self.nr_chunks)()
+            s.uarg = abi.StromCmd__MemCopySsdToGpu()
+            s.uarg.handle = self.handle
+            s.uarg.offset = s.offset
+            s.uarg.nr_chunks = self.nr_chunks
+            s.uarg.chunk_sz = BLCKSZ
+            s.uarg.relseg_sz = 0
+            s.uarg.chunk_ids = C.cast(s.chunk_ids, C.POINTER(C.c_uint32))
+            s.uarg.wb_buffer = None
+            s.event = torch.cuda.Event()
+            s.busy = False
+            s.first_page = 0
+            s.ref_host = s.ref_dev = s.wb = None
+            if verify:
+                s.ref_host = torch.empty(segment_sz, dtype=torch.uint8).pin_memory()
+                s.ref_dev = torch.empty(segment_sz, dtype=torch.uint8, device=self.device)
+            self.slots.append(s)
+
+    def close(self):
+        if self.handle:
+            uarg = abi.StromCmd__UnmapGpuMemory()
+            uarg.handle = self.handle
+            abi.nvme_strom_ioctl(abi.STROM_IOCTL__UNMAP_GPU_MEMORY, uarg)
+            self.handle = 0
+
+    # -- one segment ---------------------------------------------------------
+    def _submit(self, slot, fd, seg_index):
+        first_page = seg_index * self.nr_chunks
+        ids = np.frombuffer(slot.chunk_ids, dtype=np.uint32)
+        ids[:] = np.arange(first_page, first_page + self.nr_chunks, dtype=np.uint32)
+        slot.uarg.file_desc = fd
+        slot.first_page = first_page
+        abi.nvme_strom_ioctl(abi.STROM_IOCTL__MEMCPY_SSD2GPU, slot.uarg)
+        self.h2d_bytes += self.segment_sz
+        self.counters["nr_ram2gpu"] += slot.uarg.nr_ram2gpu
+        self.counters["nr_ssd2gpu"] += slot.uarg.nr_ssd2gpu
+        self.counters["nr_dma_submit"] += slot.uarg.nr_dma_submit
+        self.counters["nr_dma_blocks"] += slot.uarg.nr_dma_blocks
+        if self.verify:
+            # the reference's own second path: pread through the VFS (:249-252)
+            view = memoryview(slot.ref_host.numpy())
+            done = 0
+            while done < self.segment_sz:
+                n = os.preadv(fd, [view[done:]], first_page * BLCKSZ + done)
+                if n <= 0:
+                    raise IOError("short read on the verification path")
+                done += n
+        slot.busy = True
+
+    def _complete(self, slot):
+        warg = abi.StromCmd__MemCopyWait()
+        warg.dma_task_id = slot.uarg.dma_task_id
+        abi.nvme_strom_ioctl(abi.STROM_IOCTL__MEMCPY_WAIT, warg)
+        base = self.buffer.data_ptr() + slot.offset
+        st = C.c_void_p(self.stream.cuda_stream)
+        res = None
+        if self.results is not None:
+            res = C.c_void_p(self.results.data_ptr() + (slot.first_page - self.results_base) * 8)
+        with torch.cuda.stream(self.stream):
+            if self.verify:
+                slot.ref_dev.copy_(slot.ref_host, non_blocking=True)
+                self.h2d_bytes += self.segment_sz
+                abi.check(lib.strom_scan_verify_pages_dev(
+                    C.c_void_p(base), C.c_void_p(slot.ref_dev.data_ptr()), self.nr_chunks,
+                    slot.first_page & 0xFFFFFFFF, self.scan_flags, slot.first_page * BLCKSZ, res,
+                    C.c_void_p(self.totals.data_ptr()), st), "strom_scan_verify_pages_dev")
+            elif self.scan:
+                abi.check(lib.strom_scan_pages_dev(
+                    C.c_void_p(base), self.nr_chunks, slot.first_page & 0xFFFFFFFF, self.scan_flags,
+                    res, C.c_void_p(self.totals.data_ptr()), st), "strom_scan_pages_dev")
+            slot.event.record(self.stream)
+
+    # -- whole range ------------------------------------------------------------
+    def run(self, path, first_segment=0, n_segments=None):
+        """Loads segments [first_segment, first_segment + n_segments) of ``path``
+        and processes them on the GPU.  Returns (totals list, counters dict)."""
+        fd = os.open(path, os.O_RDONLY)
+        try:
+            carg = abi.StromCmd__CheckFile()
+            carg.fdesc = fd
+            abi.nvme_strom_ioctl(abi.STROM_IOCTL__CHECK_FILE, carg)
+            fsize = os.fstat(fd).st_size
+            total = fsize // self.segment_sz                  # the tail is dropped, :785
+            if n_segments is None:
+                n_segments = total - first_segment
+            if first_segment + n_segments > total:
+                raise ValueError("segment range runs past the end of the file")
+            self.counters = dict(nr_ram2gpu=0, nr_ssd2gpu=0, nr_dma_submit=0, nr_dma_blocks=0)
+            self.h2d_bytes = 0
+            if self.keep_results:
+                self.results = torch.empty(n_segments * self.nr_chunks * 4, dtype=torch.int16,
+                                           device=self.device)
+                self.results_base = first_segment * self.nr_chunks
+            abi.check(lib.strom_totals_reset_dev(C.c_void_p(self.totals.data_ptr()),
+                                                 C.c_void_p(self.stream.cuda_stream)), "reset")
+            inflight = deque()
+            for k in range(n_segments):
+                if len(inflight) == self.nr_segments:
+                    self._complete(inflight.popleft())
+                slot = self.slots[k % self.nr_segments]
+                if slot.busy:
+                    slot.event.synchronize()                  # its kernel has read the slot
+                    slot.busy = False
+                self._submit(slot, fd, first_segment + k)
+                inflight.append(slot)
+            while inflight:
+                self._complete(inflight.popleft())
+            totals = self.totals.cpu()                        # the D2H of the result
+            for s in self.slots:
+                s.busy = False
+            out = [int(x) & 0xFFFFFFFFFFFFFFFF for x in totals.tolist()]
+            return out, dict(self.counters, h2d_bytes=self.h2d_bytes, d2h_bytes=abi.T_COUNT * 8,
+                             n_segments=n_segments)
+        finally:
+            os.close(fd)
+
+    def results_host(self):
+        """per-page records (n, 4) uint16: checksum, flags, n_normal, n_bad_lp"""
+        return self.results.cpu().numpy().view(np.uint16).reshape(-1, 4)
+
+
+def heapgen_file(path, seed, n_pages, mixed=False, n_threads=None, first_page=0):
+    """Writes the SURVEY 8d synthetic heap file with the library's generator."""
+    if n_threads is None:
+        n_threads = min(os.cpu_count() or 1, 32)
+    abi.check(lib.strom_heapgen_file(path.encode(), seed, first_page, n_pages, int(mixed), n_threads),
+              "strom_heapgen_file")
+
+
+def partition_segments(n_segments, n_parts, rank):
+    first, count = C.c_uint64(), C.c_uint64()
+    abi.check(lib.strom_partition_segments(n_segments, n_parts, rank, C.byref(first), C.byref(count)),
+              "strom_partition_segments")
+    return first.value, count.value
