@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py -- the hot path's headline numbers, one JSON line.
+
+Workload (BASELINE.json configs[1], "C2"): a synthetic heap file of 8KB
+PostgreSQL pages, 1 GiB (131072 pages) per GPU, loaded in 32 MB segments over
+6 slots through MEMCPY_SSD2GPU / MEMCPY_WAIT and scanned on the GPU
+(pg_checksum_page + PageIsVerified header test + line-pointer validation).
+A "step" is one pass over the rank's 1 GiB shard.
+
+  value      page-checksum scan throughput, pages already resident in HBM
+  e2e        the same pass through the C ABI from the HOST side: file (page
+             cache) -> pinned staging -> H2D -> scan -> counters D2H, all
+             inside the timed region
+  roofline   the scan kernel against the measured HBM copy bandwidth
+  cpu_baseline / --impl reference
+             the reference's CPU path (read() into RAM, utils/nvme_test.c:
+             543-552) + the oracle's checksum/validate (the reference has no
+             such code of its own), on this box's host cores
+
+N > 1 (torchrun, one rank per GPU): every rank owns a disjoint contiguous
+segment range of one N GiB file (weak scaling), no data-path collective; the
+16 counters are merged once at the end over NCCL.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GIB = 1 << 30
+SEG = 32 << 20
+SLOTS = 6
+PAGES_PER_GIB = GIB // 8192
+SEED = 0x5EED0001
+METRIC = "page_checksum_scan_GBps"
+
+
+def env_rank():
+    return (int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")),
+            int(os.environ.get("WORLD_SIZE", "1")))
+
+
+def bench_dir(need_bytes):
+    d = os.environ.get("NVME_STROM_BENCH_DIR")
+    if d:
+        return d
+    for cand in ("/tmp", "/dev/shm"):
+        try:
+            st = os.statvfs(cand)
+            if st.f_bavail * st.f_frsize > need_bytes + (2 << 30):
+                return cand
+        except OSError:
+            pass
+    return "/tmp"
+
+
+# ---------------------------------------------------------------------------
+# clocks: NVML sampler thread running during the timed regions
+# ---------------------------------------------------------------------------
+class ClockSampler:
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {nv.nvmlClocksEventReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksEventReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksEventReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksEventReasonSwPowerCap: "sw_power_cap"}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def start(self):
+        if self.nv:
+            self._stop.clear()
+            self._thr = threading.Thread(target=self._loop, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        if self._thr:
+            self._stop.set()
+            self._thr.join()
+            self._thr = None
+
+    def summary(self):
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------
+# CPU arm: the reference's host path, restated (oracle/) -- rank 0 only
+# ---------------------------------------------------------------------------
+def cpu_path(path, max_bytes, threads, passes, do_compare=False):
+    """returns (GB/s over `passes` passes, phase seconds of the last pass)"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from conftest import Oracle            # bench.py's CPU legs may use the oracle
+    o = Oracle()
+    secs = (C.c_double * 4)()
+    tot = o.Totals()
+    done, wall = 0, 0.0
+    for _ in range(passes):
+        rc = o.lib.ora_cpu_path(path.encode(), SEG, max_bytes, threads, 1, int(do_compare), C.byref(tot), secs)
+        if rc != 0:
+            raise RuntimeError(f"ora_cpu_path failed: {rc}")
+        done += (max_bytes // SEG) * SEG
+        wall += secs[3]
+    return done / wall / 1e9, {"read_s": secs[0], "scan_s": secs[1], "compare_s": secs[2], "wall_s": secs[3]}, \
+        [int(x) for x in tot.v]
+
+
+def run_reference(args):
+    rank, _, world = env_rank()
+    if rank != 0:
+        return 0
+    from nvme_strom_b200.loader import heapgen_file
+    threads = os.cpu_count() or 1
+    path = os.path.join(bench_dir(GIB), f"strom_bench_ref_{os.getpid()}.heap")
+    heapgen_file(path, SEED, PAGES_PER_GIB)
+    try:
+        for _ in range(args.warmup):
+            cpu_path(path, GIB, threads, 1)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            gbps, phases, totals = cpu_path(path, GIB, threads, 1)
+        dt = (time.perf_counter() - t0) / args.steps
+    finally:
+        os.unlink(path)
+    val = GIB / dt / 1e9
+    line = {"impl": "reference", "metric": METRIC, "value": round(val, 3), "unit": "GB/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(dt * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": "C1/C2 CPU path: read() of a 1 GiB synthetic heap file in 32 MB pieces into RAM "
+                                   "+ checksum/validate of every page, all host threads; one step = one pass"},
+            "cpu_baseline": {"value": round(val, 3), "unit": "GB/s", "cores": threads, "kind": "port",
+                             "sample": "1 GiB per step (the whole C2 file), warm page cache"},
+            "e2e": {"value": round(val, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+def run_product(args):
+    import torch
+    import torch.distributed as dist
+
+    from nvme_strom_b200 import abi, multigpu
+    from nvme_strom_b200.abi import lib
+    from nvme_strom_b200.loader import SegmentPipeline, heapgen_file
+
+    rank, local_rank, world = env_rank()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libnvme_strom has no CPU path for the page kernels")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        ncpu = os.cpu_count() or 16
+        os.environ.setdefault("NVME_STROM_READERS", str(max(4, min(16, ncpu // world))))
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- the synthetic file: world GiB, each rank writes (and later reads) its own GiB
+    d = bench_dir(world * GIB)
+    tag = os.environ.get("MASTER_PORT", str(os.getppid() if world > 1 else os.getpid()))
+    path = os.path.join(d, f"strom_bench_{tag}.heap")
+    n_seg_total = world * GIB // SEG
+    first_seg, n_seg = multigpu.partition_segments(n_seg_total, world, rank)
+    pages_mine = n_seg * (SEG // 8192)
+    first_page = first_seg * (SEG // 8192)
+    heapgen_file(path, SEED, pages_mine, first_page=first_page)
+    barrier()
+    shard_bytes = pages_mine * 8192
+
+    sampler = ClockSampler(local_rank)
+    result = {}
+    try:
+        # ---- (1) HBM-resident scan --------------------------------------------------
+        pipe = SegmentPipeline(local_rank, SEG, SLOTS, scan=False)
+        resident = torch.empty(shard_bytes, dtype=torch.uint8, device=dev)
+        with open(path, "rb") as f:                      # plain staging of the resident copy (untimed)
+            f.seek(first_page * 8192)
+            stage = torch.empty(SEG, dtype=torch.uint8).pin_memory()
+            for k in range(n_seg):
+                f.readinto(memoryview(stage.numpy()))
+                resident[k * SEG:(k + 1) * SEG].copy_(stage, non_blocking=False)
+        totals = torch.zeros(abi.T_COUNT, dtype=torch.int64, device=dev)
+        stream = torch.cuda.Stream(device=dev)
+        p_tot, p_res, st = C.c_void_p(totals.data_ptr()), C.c_void_p(resident.data_ptr()), C.c_void_p(stream.cuda_stream)
+
+        def scan_step():
+            abi.check(lib.strom_scan_pages_dev(p_res, pages_mine, first_page & 0xFFFFFFFF, 0, None, p_tot, st),
+                      "strom_scan_pages_dev")
+
+        with torch.cuda.stream(stream):
+            abi.check(lib.strom_totals_reset_dev(p_tot, st), "reset")
+            for _ in range(max(args.warmup, 3)):
+                scan_step()
+        barrier()
+        launches0 = lib.strom_kernel_launch_count()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.start()
+        with torch.cuda.stream(stream):
+            ev0.record(stream)
+            for _ in range(args.steps):
+                scan_step()
+            ev1.record(stream)
+        barrier()
+        sampler.stop()
+        launches = lib.strom_kernel_launch_count() - launches0
+        ms_value = max_over_ranks(ev0.elapsed_time(ev1) / args.steps)
+        kernel_ms = ev0.elapsed_time(ev1) / args.steps          # one launch per step on `stream`
+        value = world * GIB / (ms_value * 1e-3) / 1e9
+
+        # ---- (2) end to end through the C ABI, host buffers -----------------------------
+        pipe.scan = True
+        for _ in range(max(args.warmup, 3)):
+            pipe.run(path, first_seg, n_seg)
+        barrier()
+        sampler.start()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_totals, counters = pipe.run(path, first_seg, n_seg)   # ends with the D2H of the counters
+        torch.cuda.synchronize()
+        t_local = (time.perf_counter() - t0) / args.steps
+        barrier()
+        sampler.stop()
+        ms_e2e = max_over_ranks(t_local * 1e3)
+        e2e = world * GIB / (ms_e2e * 1e-3) / 1e9
+
+        # ---- correctness witnesses (no oracle here): a clean file has no failures --------
+        merged = multigpu.reduce_totals(e2e_totals, dev)
+        assert merged[abi.T_PAGES] == world * PAGES_PER_GIB, merged
+        assert merged[abi.T_CHECKSUM_FAIL] == merged[abi.T_HEADER_FAIL] == merged[abi.T_INVALID] == 0, merged
+        assert merged[abi.T_LP_BAD_PAGES] == 0 and merged[abi.T_N_NORMAL] > 0, merged
+
+        # ---- (3) extras: load only, and the byte-compare verify (config C2's second half) --
+        extras = {}
+        if world == 1 and not args.quick:
+            pipe.scan = False
+            pipe.run(path, first_seg, n_seg)
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                pipe.run(path, first_seg, n_seg)
+            torch.cuda.synchronize()
+            extras["load_only_GBps"] = round(GIB / ((time.perf_counter() - t0) / args.steps) / 1e9, 2)
+            ref = resident.clone()
+            for name, fn, nbytes in (
+                ("verify_kernel_GBps", lambda: lib.strom_verify_pages_dev(p_res, C.c_void_p(ref.data_ptr()), pages_mine, None, 0, p_tot, st), 2 * GIB),
+                ("fused_scan_verify_GBps", lambda: lib.strom_scan_verify_pages_dev(p_res, C.c_void_p(ref.data_ptr()), pages_mine, 0, 0, 0, None, p_tot, st), 2 * GIB)):
+                with torch.cuda.stream(stream):
+                    for _ in range(3):
+                        fn()
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record(stream)
+                    for _ in range(args.steps):
+                        fn()
+                    b.record(stream)
+                torch.cuda.synchronize()
+                extras[name] = round(nbytes / (a.elapsed_time(b) / args.steps * 1e-3) / 1e9, 1)
+            del ref
+            vp = SegmentPipeline(local_rank, SEG, SLOTS, verify=True)
+            vp.run(path, first_seg, n_seg)
+            t0 = time.perf_counter()
+            for _ in range(max(2, args.steps // 4)):
+                vt, _ = vp.run(path, first_seg, n_seg)
+            torch.cuda.synchronize()
+            extras["e2e_with_byte_compare_GBps"] = round(GIB / ((time.perf_counter() - t0) / max(2, args.steps // 4)) / 1e9, 2)
+            assert vt[abi.T_MISMATCH_BLOCKS] == 0
+            vp.close()
+        pipe.close()
+
+        # ---- roofline of the dominant kernel ------------------------------------------------
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = pages_mine * 8192 / (kernel_ms * 1e-3) / 1e9
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_kernel_ncu_summary.json"))).get(
+                "dram_bytes_per_launch_1GiB")
+        except Exception:
+            pass
+        result = {
+            "metric": METRIC, "value": round(value, 2), "unit": "GB/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_value, 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
+            "data": "synthetic",
+            "config": {"workload": "C2: 1 GiB synthetic PG heap file per GPU (131072 x 8KB pages, seed 0x5EED0001), "
+                                   "32 MB segments x 6 slots, checksum + header + line-pointer scan",
+                       "file_dir": d, "page_cache": "warm", "l2": "input (1 GiB) >> L2 (126 MB), no flush needed",
+                       "parallelism": f"{world} x independent shard, counters merged once",
+                       "readers": os.environ.get("NVME_STROM_READERS", "default")},
+            "e2e": {"value": round(e2e, 2), "unit": "GB/s", "ms_per_step": round(ms_e2e, 3),
+                    "h2d_bytes_per_step": int(counters["h2d_bytes"]), "d2h_bytes_per_step": int(counters["d2h_bytes"])},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "scan_ldg_kernel<8,false,2>", "achieved": round(achieved, 1),
+                         "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                         "algorithmic_bytes_per_launch": pages_mine * 8192},
+            "clocks": sampler.summary(),
+        }
+        result.update(extras)
+    finally:
+        barrier()
+        if rank == 0:
+            try:
+                os.unlink(path)
+            except OSError:
+                pass
+
+    # ---- CPU baseline beside it: rank 0, N = 1 only, bounded sample -------------------------
+    if world == 1 and rank == 0 and not args.no_cpu:
+        heapgen_file(path, SEED, PAGES_PER_GIB)
+        try:
+            threads = os.cpu_count() or 1
+            one_gbps, one_ph, _ = cpu_path(path, 256 << 20, 1, 1, do_compare=True)
+            cpu_path(path, GIB, threads, 1)
+            passes = 6
+            all_gbps, all_ph, _ = cpu_path(path, GIB, threads, passes)
+            result["cpu_baseline"] = {
+                "value": round(all_gbps, 3), "unit": "GB/s", "cores": threads, "kind": "port",
+                "sample": f"{passes} passes over the 1 GiB file (read + checksum/validate, no compare), warm page cache",
+                "single_thread_GBps": round(one_gbps, 3),
+                "single_thread_phases_256MiB": {k: round(v, 4) for k, v in one_ph.items()}}
+        finally:
+            os.unlink(path)
+    if rank == 0:
+        print(json.dumps(result))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--quick", action="store_true", help="skip the extra verify/load-only measurements")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_product(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

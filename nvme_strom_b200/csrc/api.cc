@@ -427,6 +427,7 @@ using namespace strom;
 
 extern "C" int nvme_strom_ioctl_on(int token, int cmd, void *arg)
 {
+	const int saved_errno = errno;
 	clear_error();
 	int rc = dispatch(token, cmd, arg);
 	if (rc < 0)
@@ -434,6 +435,7 @@ extern "C" int nvme_strom_ioctl_on(int token, int cmd, void *arg)
 		errno = -rc;
 		return -1;
 	}
+	errno = saved_errno;                  /* like ioctl(2): success leaves errno untouched */
 	return 0;
 }
 

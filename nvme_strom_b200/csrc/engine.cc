@@ -21,9 +21,11 @@
  * SSD2RAM pieces have a host destination: pread straight into the caller's
  * DMA buffer, no staging (kmod/nvme_strom.c:1693-1761).
  *
- * Environment: NVME_STROM_READERS (threads per engine, default 12),
- * NVME_STROM_SLOT_KB (staging slot, default 1024), NVME_STROM_SLOTS (per
- * thread, default 3), NVME_STROM_HOST_READERS (SSD2RAM threads, default 8).
+ * Environment: NVME_STROM_READERS (threads per engine, default min(16, cpus/2):
+ * the other half of the cores is left to the caller and the CUDA driver),
+ * NVME_STROM_SLOT_KB (staging slot, default 4096), NVME_STROM_SLOTS (per
+ * thread, default 2), NVME_STROM_HOST_READERS (SSD2RAM threads, default
+ * min(8, cpus)).  Defaults from the sweep in profiles/r01_xfer_sweep.txt.
  */
 #include "strom_internal.h"
 #include <cstring>
@@ -44,7 +46,7 @@ static int env_int(const char *name, int dflt, int lo, int hi)
 
 uint32_t engine_piece_max()
 {
-	static uint32_t v = (uint32_t)env_int("NVME_STROM_SLOT_KB", 1024, 128, 65536) << 10;
+	static uint32_t v = (uint32_t)env_int("NVME_STROM_SLOT_KB", 4096, 128, 65536) << 10;
 	return v;
 }
 
@@ -77,8 +79,10 @@ public:
 	Engine(int device, void *ctx, bool host_only)
 		: device_(device), ctx_(ctx), host_only_(host_only)
 	{
-		int n = host_only ? env_int("NVME_STROM_HOST_READERS", 8, 1, 256)
-						  : env_int("NVME_STROM_READERS", 12, 1, 256);
+		int ncpu = (int)std::thread::hardware_concurrency();
+		if (ncpu < 1) ncpu = 8;
+		int n = host_only ? env_int("NVME_STROM_HOST_READERS", std::min(ncpu, 8), 1, 256)
+						  : env_int("NVME_STROM_READERS", std::max(2, std::min(ncpu / 2, 16)), 1, 256);
 		for (int i = 0; i < n; i++)
 			threads_.emplace_back([this, i] { worker(i); });
 	}
@@ -157,7 +161,7 @@ private:
 		const DriverApi &api = driver_api();
 		const bool bound = (ctx_ && api.ok && api.cuCtxSetCurrent(ctx_) == 0) ||
 					   cudaSetDevice(device_) == cudaSuccess;
-		const int n_slots = env_int("NVME_STROM_SLOTS", 3, 2, 16);
+		const int n_slots = env_int("NVME_STROM_SLOTS", 2, 2, 16);
 		const uint32_t slot_sz = engine_piece_max();
 		std::vector<Slot> slots((size_t)n_slots);
 		cudaStream_t stream = nullptr;

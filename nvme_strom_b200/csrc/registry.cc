@@ -394,6 +394,12 @@ void task_put(DmaTask *t, long status)
 	/* last reference: retire (strom_put_dma_task, kmod/nvme_strom.c:688-728) */
 	TaskStripe &s = stripe_of(t->id);
 	const long final_status = t->status.load();
+	if (stat_info_level() > 0)             /* before the wake-up: a waiter may read STAT_INFO next */
+	{
+		uint64_t now = rdtsc_now();
+		g_stats.nr_ssd2gpu++;
+		g_stats.clk_ssd2gpu += now > t->tsc_start ? now - t->tsc_start : 0;
+	}
 	{
 		std::lock_guard<std::mutex> g(s.lock);
 		s.running.erase(t->id);
@@ -408,12 +414,6 @@ void task_put(DmaTask *t, long status)
 		close(t->fd);
 	if (t->fd_direct >= 0)
 		close(t->fd_direct);
-	if (stat_info_level() > 0)
-	{
-		uint64_t now = rdtsc_now();
-		g_stats.nr_ssd2gpu++;
-		g_stats.clk_ssd2gpu += now > t->tsc_start ? now - t->tsc_start : 0;
-	}
 	delete t;
 }
 

@@ -165,7 +165,8 @@ class SegmentPipeline:
                 inflight.append(slot)
             while inflight:
                 self._complete(inflight.popleft())
-            totals = self.totals.cpu()                        # the D2H of the result
+            with torch.cuda.stream(self.stream):
+                totals = self.totals.cpu()                    # the D2H of the result, stream-ordered
             for s in self.slots:
                 s.busy = False
             out = [int(x) & 0xFFFFFFFFFFFFFFFF for x in totals.tolist()]
