@@ -107,6 +107,46 @@ int strom_verify_pages(unsigned long handle_a, size_t offset_a,
 					   uint64_t n_blocks, const uint32_t *h_map,
 					   StromScanTotals *h_totals);
 
+/* ---- scan for callers that must not allocate --------------------------------
+ *
+ * No counterpart in the reference: this entry point exists only here.
+ *
+ * strom_scan_pages() above keeps its device-side counters and its per-page
+ * result staging in memory it obtains with cudaMalloc (and re-obtains with
+ * cudaFree + cudaMalloc when a larger request arrives).  Some users of this
+ * library cannot afford that: a process whose device memory has been handed
+ * out in full to a pool or a fixed budget up front (a database backend with a
+ * GPU memory quota, a job sharing the device with a caching allocator) would
+ * see the allocation fail or eat into somebody else's share, and a caller on a
+ * latency-critical path cannot accept the device-wide synchronisation that
+ * cudaMalloc and cudaFree imply.  For them this variant does the same scan
+ * with the scratch placed in a fixed array that is part of the library image:
+ * it calls no cudaMalloc, no cudaFree and no allocating library routine.
+ *
+ * The price is a hard limit and a shared buffer:
+ *  - at most STROM_STATIC_SCRATCH_MAX_PAGES pages per call (1 GiB of pages);
+ *    a larger n_pages is refused with -1 / EINVAL and a message in
+ *    strom_last_error() -- split the range and merge with strom_totals_merge();
+ *  - the array (1 MiB + 256 bytes) is resident on every GPU that loads the
+ *    library, until the process exits;
+ *  - all calls on one device use the same array.  The counters are cleared at
+ *    the start of every call and every page record up to n_pages is rewritten,
+ *    so a call never sees the previous one's values -- but two calls that are
+ *    in flight on the same GPU at the same time (two threads, two streams)
+ *    overwrite each other: serialise them;
+ *  - the first call on each device looks up the device address of the array
+ *    (once, with that device current).  Make that first call during start-up,
+ *    before any stream capture begins on the device.
+ *
+ * d_pages: device pointer, 16-byte aligned, on the current device.  h_results
+ * (may be NULL) and h_totals are HOST pointers; the call returns when they are
+ * filled.  Work is ordered on `stream` (NULL = default stream).  Results are
+ * identical to strom_scan_pages_dev() / strom_scan_pages().
+ */
+#define STROM_STATIC_SCRATCH_MAX_PAGES 131072u
+int strom_scan_pages_static(const void *d_pages, uint64_t n_pages, uint32_t first_blkno,
+							StromPageResult *h_results, StromScanTotals *h_totals, void *stream);
+
 /* ---- host helpers ---------------------------------------------------------- */
 
 /* text dump around the first differing 16-byte unit, format of

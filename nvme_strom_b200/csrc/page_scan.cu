@@ -27,6 +27,7 @@
 #include "page_math.cuh"
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 namespace strom {
 
@@ -476,4 +477,88 @@ extern "C" int strom_scan_verify_pages_dev(const void *d_pages, const void *d_re
 	if (e && atoi(e) == 2)
 		return launch_ldg<2, true, 2>(d, 14, a, (cudaStream_t)stream);
 	return launch_ldg<4, true, 2>(d, 15, a, (cudaStream_t)stream);
+}
+
+/* ------------------------------------------------------------------ */
+/* scan with no allocation at all (include/strom_scan.h explains who    */
+/* needs it).  Same kernel as strom_scan_pages_dev(); only the place    */
+/* where the counters and the per-page records are staged differs: a    */
+/* fixed array inside the library image instead of cudaMalloc'ed memory. */
+/* ------------------------------------------------------------------ */
+namespace strom {
+
+constexpr size_t kStaticTotalsBytes = 256;      /* StromScanTotals (128 B), padded to the alignment */
+constexpr size_t kStaticScratchBytes =
+	kStaticTotalsBytes + (size_t)STROM_STATIC_SCRATCH_MAX_PAGES * sizeof(StromPageResult);
+
+/* One instance per GPU that loads this module, alive until the process ends.
+ * In HOST code this name is only a handle for cudaGetSymbolAddress(): it is
+ * not a device address and must never be handed to a kernel as one. */
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+static std::mutex g_static_lock;
+static unsigned char *g_static_addr[64];        /* device address of the array, per device */
+
+/* once per device, with that device current */
+static unsigned char *static_scratch_of_current_device()
+{
+	int dev = -1;
+	if (cuda_failed(cudaGetDevice(&dev), "cudaGetDevice") || dev < 0 || dev >= 64)
+		return nullptr;
+	std::lock_guard<std::mutex> g(g_static_lock);
+	if (!g_static_addr[dev])
+	{
+		unsigned char *ptr = nullptr;
+		if (cuda_failed(cudaGetSymbolAddress((void **)&ptr, g_static_scratch), "cudaGetSymbolAddress(scratch)"))
+			return nullptr;
+		g_static_addr[dev] = ptr;
+	}
+	return g_static_addr[dev];
+}
+
+} /* namespace strom */
+
+extern "C" int strom_scan_pages_static(const void *d_pages, uint64_t n_pages, uint32_t first_blkno,
+									   StromPageResult *h_results, StromScanTotals *h_totals, void *stream)
+{
+	clear_error();
+	if (!h_totals || (n_pages > 0 && (!d_pages || ((uintptr_t)d_pages & 15))))
+	{
+		set_error("strom_scan_pages_static: null or misaligned pointer");
+		errno = EINVAL;
+		return -1;
+	}
+	if (n_pages > STROM_STATIC_SCRATCH_MAX_PAGES)
+	{
+		set_error("strom_scan_pages_static: %llu pages in one call, the static scratch holds at most %u "
+				  "(STROM_STATIC_SCRATCH_MAX_PAGES); split the range",
+				  (unsigned long long)n_pages, STROM_STATIC_SCRATCH_MAX_PAGES);
+		errno = EINVAL;
+		return -1;
+	}
+	unsigned char *scratch = static_scratch_of_current_device();
+	DeviceInfo *d = device_info();
+	if (!scratch || !d)
+		return -1;
+	unsigned long long *d_totals = reinterpret_cast<unsigned long long *>(scratch);
+	StromPageResult *d_results = reinterpret_cast<StromPageResult *>(scratch + kStaticTotalsBytes);
+	cudaStream_t st = (cudaStream_t)stream;
+
+	/* the array still holds the previous call's counters: they must start from zero */
+	totals_reset_kernel<<<1, 32, 0, st>>>(d_totals);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	if (n_pages > 0)
+	{
+		ScanArgs a = {(const uint4 *)d_pages, nullptr, n_pages, 0, first_blkno,
+					  h_results ? d_results : nullptr, d_totals};
+		if (launch_ldg<8, false, 2>(d, 12, a, st) != 0)
+			return -1;
+	}
+	STROM_CUDA_OR_FAIL(cudaMemcpyAsync(h_totals, d_totals, sizeof(StromScanTotals), cudaMemcpyDeviceToHost, st));
+	if (h_results && n_pages > 0)
+		STROM_CUDA_OR_FAIL(cudaMemcpyAsync(h_results, d_results, n_pages * sizeof(StromPageResult),
+										   cudaMemcpyDeviceToHost, st));
+	STROM_CUDA_OR_FAIL(cudaStreamSynchronize(st));
+	return 0;
 }
