@@ -138,26 +138,27 @@ def run_reference(args):
         return 0
     from nvme_strom_b200.loader import heapgen_file
     threads = os.cpu_count() or 1
-    path = os.path.join(bench_dir(GIB), f"strom_bench_ref_{os.getpid()}.heap")
-    heapgen_file(path, SEED, PAGES_PER_GIB)
+    nbytes = max(1, args.gpus) * GIB            # the whole job of the GPU arm at this N
+    path = os.path.join(bench_dir(nbytes), f"strom_bench_ref_{os.getpid()}.heap")
+    heapgen_file(path, SEED, nbytes // 8192)
     try:
         for _ in range(args.warmup):
-            cpu_path(path, GIB, threads, 1)
+            cpu_path(path, nbytes, threads, 1)
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            gbps, phases, totals = cpu_path(path, GIB, threads, 1)
+            gbps, phases, totals = cpu_path(path, nbytes, threads, 1)
         dt = (time.perf_counter() - t0) / args.steps
     finally:
         os.unlink(path)
-    val = GIB / dt / 1e9
+    val = nbytes / dt / 1e9
     line = {"impl": "reference", "metric": METRIC, "value": round(val, 3), "unit": "GB/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(dt * 1e3, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": {"workload": "C1/C2 CPU path: read() of a 1 GiB synthetic heap file in 32 MB pieces into RAM "
-                                   "+ checksum/validate of every page, all host threads; one step = one pass"},
+            "config": {"workload": f"C1/C2 CPU path: read() of a {max(1, args.gpus)} GiB synthetic heap file in 32 MB pieces "
+                                   "into RAM + checksum/validate of every page, all host threads; one step = one pass"},
             "cpu_baseline": {"value": round(val, 3), "unit": "GB/s", "cores": threads, "kind": "port",
-                             "sample": "1 GiB per step (the whole C2 file), warm page cache"},
+                             "sample": f"{max(1, args.gpus)} GiB per step (the GPU arm's whole job at this N), warm page cache"},
             "e2e": {"value": round(val, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -332,7 +333,8 @@ def run_product(args):
                        "parallelism": f"{world} x independent shard, counters merged once",
                        "readers": os.environ.get("NVME_STROM_READERS", "default")},
             "e2e": {"value": round(e2e, 2), "unit": "GB/s", "ms_per_step": round(ms_e2e, 3),
-                    "h2d_bytes_per_step": int(counters["h2d_bytes"]), "d2h_bytes_per_step": int(counters["d2h_bytes"])},
+                    "h2d_bytes_per_step": int(counters["h2d_bytes"]) * world,
+                    "d2h_bytes_per_step": int(counters["d2h_bytes"]) * world},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "scan_ldg_kernel<8,false,2>", "achieved": round(achieved, 1),
                          "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,

@@ -207,7 +207,7 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 	in.file = &finfo;
 	in.page_state = split ? state.data() : nullptr;
 	in.n_state_pages = state.size();
-	in.piece_max = engine_piece_max();
+	in.piece_max = engine_piece_for((uint64_t)arg->nr_chunks * arg->chunk_sz);
 	Plan plan;
 	if ((rc = plan_chunks(in, &plan)) != 0)
 		return rc;

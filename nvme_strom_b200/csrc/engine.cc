@@ -50,6 +50,26 @@ uint32_t engine_piece_max()
 	return v;
 }
 
+static int gpu_reader_count()
+{
+	int ncpu = (int)std::thread::hardware_concurrency();
+	if (ncpu < 1) ncpu = 8;
+	return env_int("NVME_STROM_READERS", std::max(2, std::min(ncpu / 2, 16)), 1, 256);
+}
+
+/* A request smaller than readers x slot would keep most readers idle if it were cut into
+ * slot-sized pieces (a 4MB segment = one piece).  Cut it so that every reader gets one,
+ * but not below 256KB, where the per-copy cost of the DMA engine starts to show. */
+uint32_t engine_piece_for(uint64_t request_bytes)
+{
+	const uint32_t cap = engine_piece_max();
+	uint64_t per_reader = request_bytes / (uint64_t)gpu_reader_count();
+	per_reader &= ~(uint64_t)(128 * 1024 - 1);
+	if (per_reader >= cap)
+		return cap;
+	return (uint32_t)std::max<uint64_t>(per_reader, 256 * 1024);
+}
+
 static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
 {
 	uint32_t done = 0;
@@ -81,8 +101,7 @@ public:
 	{
 		int ncpu = (int)std::thread::hardware_concurrency();
 		if (ncpu < 1) ncpu = 8;
-		int n = host_only ? env_int("NVME_STROM_HOST_READERS", std::min(ncpu, 8), 1, 256)
-						  : env_int("NVME_STROM_READERS", std::max(2, std::min(ncpu / 2, 16)), 1, 256);
+		int n = host_only ? env_int("NVME_STROM_HOST_READERS", std::min(ncpu, 8), 1, 256) : gpu_reader_count();
 		for (int i = 0; i < n; i++)
 			threads_.emplace_back([this, i] { worker(i); });
 	}

@@ -39,6 +39,7 @@ struct ScanArgs {
 	uint32_t first_blkno;
 	StromPageResult *results;    /* may be null */
 	unsigned long long *totals;
+	unsigned long long *tile_counter;   /* dynamic scheduling only: next warp tile, starts at 0 */
 };
 
 /* ------------------------------------------------------------------ */
@@ -184,7 +185,7 @@ scan_tma_kernel(ScanArgs a)
 /* ------------------------------------------------------------------ */
 constexpr int kLdgThreads = 256;
 
-template <int R, bool VERIFY, int MINB>
+template <int R, bool VERIFY, int MINB, bool DYN = false>
 __global__ void __launch_bounds__(kLdgThreads, MINB)
 scan_ldg_kernel(ScanArgs a)
 {
@@ -216,10 +217,13 @@ scan_ldg_kernel(ScanArgs a)
 		}
 		for (;;)
 		{
-			const uint64_t npage = page + n_groups, nwpage = wpage + n_groups;
-			const bool nvalid = npage < a.n_pages, more = nwpage < a.n_pages;
+			uint64_t npage = page + n_groups, nwpage = wpage + n_groups;
+			bool nvalid = npage < a.n_pages, more = nwpage < a.n_pages;
 			const uint4 *np = a.pages + (nvalid ? npage : a.n_pages - 1) * 512 + k;
 			const uint4 *nq = VERIFY ? a.ref + (nvalid ? npage : a.n_pages - 1) * 512 + k : nullptr;
+			unsigned long long ticket = 0;
+			if (DYN && lane == 0)            /* ask early, read late: the atomic's latency is hidden */
+				ticket = atomicAdd(a.tile_counter, 1ull);
 			uint32_t s0 = seed0, s1 = seed1, s2 = seed2, s3 = seed3;
 			uint32_t orv = 0, cnt = 0, first_unit = 0xFFFFu;
 			PageHeader h;
@@ -237,13 +241,26 @@ scan_ldg_kernel(ScanArgs a)
 						if (VERIFY) rnxt[r] = ldg_stream(q + ((b + 1) * R + r) * 8);
 					}
 				}
-				else if (more)
+				else
 				{
-#pragma unroll
-					for (int r = 0; r < R; r++)
+					if (DYN)
 					{
-						nxt[r] = ldg_stream(np + r * 8);
-						if (VERIFY) rnxt[r] = ldg_stream(nq + r * 8);
+						ticket = __shfl_sync(FULL, ticket, 0);
+						nwpage = (ticket + (n_groups >> 2)) * 4;
+						npage = nwpage + (lane >> 3);
+						nvalid = npage < a.n_pages;
+						more = nwpage < a.n_pages;
+						np = a.pages + (nvalid ? npage : a.n_pages - 1) * 512 + k;
+						if (VERIFY) nq = a.ref + (nvalid ? npage : a.n_pages - 1) * 512 + k;
+					}
+					if (more)
+					{
+#pragma unroll
+						for (int r = 0; r < R; r++)
+						{
+							nxt[r] = ldg_stream(np + r * 8);
+							if (VERIFY) rnxt[r] = ldg_stream(nq + r * 8);
+						}
 					}
 				}
 				if (b == 0)
@@ -318,6 +335,107 @@ scan_ldg_kernel(ScanArgs a)
 	flush_totals(acc, k == 0, s_tot, a.totals);
 }
 
+/* ------------------------------------------------------------------ */
+/* kernel 3: one warp per page, lane j = column j, whole page in registers */
+/*                                                                        */
+/* The time a launch loses at its end is about one "page time" (how long  */
+/* one page stays in flight), and a page's time in flight is              */
+/* 8KB x concurrent pages / bandwidth.  Kernel 2 keeps ~9500 pages in     */
+/* flight (11 us each); this one keeps ~1800 (148 SMs x W warps), each    */
+/* fully requested at once: 64 coalesced 128-byte warp loads per page,    */
+/* the next page's 64 words per lane requested while the current 64 are   */
+/* hashed.  Same arithmetic, same outputs.                                */
+/* ------------------------------------------------------------------ */
+__device__ __forceinline__ uint32_t ldg32_stream(const uint32_t *p)
+{
+	uint32_t r;
+	asm("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+	return r;
+}
+
+template <bool VERIFY>
+__device__ __forceinline__ void
+col_process_page(const ScanArgs &a, uint64_t page, uint32_t lane, uint32_t seed,
+				 const uint32_t (&cur)[64], uint32_t (&nxt)[64], const uint32_t *next_ptr, bool have_next,
+				 TotalsAcc &acc)
+{
+	const PageHeader h = decode_header(__shfl_sync(0xFFFFFFFFu, cur[0], 2), __shfl_sync(0xFFFFFFFFu, cur[0], 3),
+									   __shfl_sync(0xFFFFFFFFu, cur[0], 4));
+	const uint32_t lp_end = kHdrWords + h.nlp;
+	uint32_t sum = seed, orv = 0, cnt = 0;
+
+#pragma unroll
+	for (int q = 0; q < 4; q++)
+	{
+		if (have_next)
+		{
+#pragma unroll
+			for (int r = 0; r < 16; r++)
+				nxt[q * 16 + r] = ldg32_stream(next_ptr + (q * 16 + r) * 32);
+		}
+#pragma unroll
+		for (int r = 0; r < 16; r++)
+		{
+			const uint32_t row = q * 16 + r;
+			uint32_t w = cur[row];
+			orv |= w;
+			if (row * 32 < lp_end)                                     /* warp-uniform */
+			{
+				const uint32_t widx = row * 32 + lane;
+				if (widx >= kHdrWords && widx < lp_end)
+					cnt += lp_check(w, h);
+			}
+			if (row == 0 && lane == 2)
+				w &= 0xFFFF0000u;                                      /* pd_checksum := 0 */
+			sum = fnv_mix(sum, w);
+		}
+	}
+	sum = fnv_mix(fnv_mix(sum, 0), 0);
+	const uint32_t hash = __reduce_xor_sync(0xFFFFFFFFu, sum);
+	const uint32_t any = __reduce_or_sync(0xFFFFFFFFu, orv);
+	cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
+	if (lane == 0)
+	{
+		StromPageResult r = finish_page(hash, a.first_blkno + (uint32_t)page, any == 0, h, cnt);
+		if (a.results)
+			a.results[page] = r;
+		acc.add(r);
+	}
+}
+
+template <int W>
+__global__ void __launch_bounds__(W * 32, 1)
+scan_col_kernel(ScanArgs a)
+{
+	__shared__ unsigned long long s_tot[STROM_T_COUNT];
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint64_t stride = (uint64_t)gridDim.x * W;
+	uint64_t page = (uint64_t)blockIdx.x * W + warp;
+	const uint32_t *base = reinterpret_cast<const uint32_t *>(a.pages) + lane;
+	const uint32_t seed = kLaneSeed[lane];
+	TotalsAcc acc;
+	uint32_t bufa[64], bufb[64];
+
+	if (page < a.n_pages)
+	{
+#pragma unroll
+		for (int i = 0; i < 64; i++)
+			bufa[i] = ldg32_stream(base + page * kPageWords + i * 32);
+	}
+	while (page < a.n_pages)
+	{
+		uint64_t np = page + stride;
+		col_process_page<false>(a, page, lane, seed, bufa, bufb, base + np * kPageWords, np < a.n_pages, acc);
+		page = np;
+		if (page >= a.n_pages)
+			break;
+		np = page + stride;
+		col_process_page<false>(a, page, lane, seed, bufb, bufa, base + np * kPageWords, np < a.n_pages, acc);
+		page = np;
+	}
+	flush_totals(acc, lane == 0, s_tot, a.totals);
+}
+
 __global__ void totals_reset_kernel(unsigned long long *t)
 {
 	if (threadIdx.x < STROM_T_COUNT)
@@ -349,12 +467,14 @@ static DeviceInfo *device_info()
 
 /* NVME_STROM_SCAN_VARIANT = "tma:W:S" (warps, slots per warp) | "ldg:R:B" (rows
  * in flight, min blocks per SM); default picked by measurement */
-struct Variant { bool tma; int a, b; };
+struct Variant { bool tma; int a, b; bool dyn = false; bool col = false; };
 static Variant pick_variant(uint32_t flags)
 {
 	Variant v = {false, 8, 2};      /* measured on B200: ldg:8:2 reaches 0.97 of the copy peak */
 	const char *e = getenv("NVME_STROM_SCAN_VARIANT");
 	if (e && !strncmp(e, "tma:", 4)) { v.tma = true; sscanf(e + 4, "%d:%d", &v.a, &v.b); }
+	else if (e && !strncmp(e, "col:", 4)) { v.tma = false; v.col = true; v.a = atoi(e + 4); }
+	else if (e && !strncmp(e, "ldgdyn", 6)) { v.tma = false; v.a = 8; v.b = 2; v.dyn = true; }
 	else if (e && !strncmp(e, "ldg:", 4)) { v.tma = false; v.a = 8; v.b = 2; sscanf(e + 4, "%d:%d", &v.a, &v.b); }
 	if (flags & STROM_SCAN_KERNEL_LDG) { if (v.tma) { v.tma = false; v.a = 8; v.b = 2; } }
 	if (flags & STROM_SCAN_KERNEL_TMA) { if (!v.tma) { v.tma = true; v.a = 8; v.b = 3; } }
@@ -379,22 +499,44 @@ static int launch_tma(DeviceInfo *d, int slot, const ScanArgs &a, cudaStream_t s
 	return 0;
 }
 
-template <int R, bool V, int MINB>
-static int launch_ldg(DeviceInfo *d, int slot, const ScanArgs &a, cudaStream_t st)
+template <int R, bool V, int MINB, bool DYN = false>
+static int launch_ldg(DeviceInfo *d, int slot, const ScanArgs &a_in, cudaStream_t st)
 {
+	ScanArgs a = a_in;
+	if (DYN)
+	{
+		/* experiment: library-owned ticket counter, zeroed in stream order before the launch */
+		static unsigned long long *counter[64];
+		int dv = (int)(d - g_dev);
+		if (!counter[dv])
+			STROM_CUDA_OR_FAIL(cudaMalloc((void **)&counter[dv], 256));
+		STROM_CUDA_OR_FAIL(cudaMemsetAsync(counter[dv], 0, 8, st));
+		a.tile_counter = counter[dv];
+	}
 	static int occ[64][16];
 	int dev = (int)(d - g_dev);
 	if (occ[dev][slot] == 0)
 	{
 		int n = 0;
-		STROM_CUDA_OR_FAIL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_ldg_kernel<R, V, MINB>,
+		STROM_CUDA_OR_FAIL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_ldg_kernel<R, V, MINB, DYN>,
 																		 kLdgThreads, 0));
 		occ[dev][slot] = n > 0 ? n : 1;
 	}
 	uint64_t want = (a.n_pages * 8 + kLdgThreads - 1) / kLdgThreads;
 	uint64_t cap = (uint64_t)d->sm_count * occ[dev][slot];
 	int grid = (int)(want < cap ? want : cap);
-	scan_ldg_kernel<R, V, MINB><<<grid, kLdgThreads, 0, st>>>(a);
+	scan_ldg_kernel<R, V, MINB, DYN><<<grid, kLdgThreads, 0, st>>>(a);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	return 0;
+}
+
+template <int W>
+static int launch_col(DeviceInfo *d, const ScanArgs &a, cudaStream_t st)
+{
+	uint64_t want = (a.n_pages + W - 1) / W;
+	int grid = (int)(want < (uint64_t)d->sm_count ? want : (uint64_t)d->sm_count);
+	scan_col_kernel<W><<<grid, W * 32, 0, st>>>(a);
 	g_kernel_launches++;
 	STROM_CUDA_OR_FAIL(cudaGetLastError());
 	return 0;
@@ -450,6 +592,16 @@ extern "C" int strom_scan_pages_dev(const void *d_pages, uint64_t n_pages, uint3
 		if (v.a == 14 && v.b == 2) return launch_tma<14, 2>(d, 6, a, st);
 		return launch_tma<8, 3>(d, 7, a, st);
 	}
+	if (v.col)
+	{
+		if (v.a == 8)  return launch_col<8>(d, a, st);
+		if (v.a == 10) return launch_col<10>(d, a, st);
+		if (v.a == 6)  return launch_col<6>(d, a, st);
+		if (v.a == 4)  return launch_col<4>(d, a, st);
+		return launch_col<12>(d, a, st);
+	}
+	if (v.dyn)                 return launch_ldg<8, false, 2, true>(d, 7, a, st);
+	if (v.a == 16 && v.b == 1) return launch_ldg<16, false, 1>(d, 8, a, st);
 	if (v.a == 4 && v.b == 1)  return launch_ldg<4, false, 1>(d, 8, a, st);
 	if (v.a == 8 && v.b == 1)  return launch_ldg<8, false, 1>(d, 9, a, st);
 	if (v.a == 4 && v.b == 3)  return launch_ldg<4, false, 3>(d, 10, a, st);

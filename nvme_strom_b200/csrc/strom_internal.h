@@ -126,6 +126,7 @@ Engine *engine_for_window(const GpuWindow &w);            /* created on demand  
 Engine *engine_for_host();
 void engine_submit(Engine *e, const std::vector<Job> &jobs);
 uint32_t engine_piece_max();                              /* staging slot size   */
+uint32_t engine_piece_for(uint64_t request_bytes);        /* piece size for one request */
 
 /* ---- statistics (kmod/nvme_strom.c:64-86) --------------------------------------- */
 struct Stats {

@@ -10,6 +10,7 @@ torch is used for device memory, streams and events only.  Every operation on
 the data goes through the C ABI of libnvme_strom.
 """
 import ctypes as C
+import mmap
 import os
 from collections import deque
 
@@ -24,14 +25,17 @@ BLCKSZ = abi.BLCKSZ
 
 class _Slot:
     __slots__ = ("index", "offset", "chunk_ids", "uarg", "event", "busy", "first_page", "ref_host",
-                 "ref_dev", "wb")
+                 "ref_dev", "wb", "ram_ids", "ram_arg")
 
 
 class SegmentPipeline:
     """N in-flight segments of ``segment_sz`` bytes landing in one mapped device buffer."""
 
     def __init__(self, device=0, segment_sz=32 << 20, nr_segments=6, verify=False, scan=True,
-                 scan_flags=abi.SCAN_DEFAULT, keep_results=False):
+                 scan_flags=abi.SCAN_DEFAULT, keep_results=False, via_ram=False):
+        """verify: also fetch every segment a second way (MEMCPY_SSD2RAM + H2D) and byte-compare
+        the two copies on the GPU.  via_ram: do not use MEMCPY_SSD2GPU at all -- land in a host
+        DMA buffer with MEMCPY_SSD2RAM and copy up from there (config C4's comparison arm)."""
         if segment_sz % BLCKSZ:
             raise ValueError("segment size must be a multiple of 8192")
         self.device = torch.device("cuda", device)
@@ -39,7 +43,8 @@ class SegmentPipeline:
         self.segment_sz = segment_sz
         self.nr_segments = nr_segments
         self.nr_chunks = segment_sz // BLCKSZ
-        self.verify = verify
+        self.verify = verify and not via_ram
+        self.via_ram = via_ram
         self.scan = scan
         self.scan_flags = scan_flags
         self.keep_results = keep_results
@@ -54,6 +59,7 @@ class SegmentPipeline:
         self.handle = marg.handle
         self.h2d_bytes = 0
         self.slots = []
+        self._dma_maps = []
         for i in range(nr_segments):
             s = _Slot()
             s.index = i
@@ -71,12 +77,37 @@ class SegmentPipeline:
             s.busy = False
             s.first_page = 0
             s.ref_host = s.ref_dev = s.wb = None
-            if verify:
-                s.ref_host = torch.empty(segment_sz, dtype=torch.uint8).pin_memory()
+            if verify or via_ram:
+                s.ref_host = self._alloc_dma_buffer(segment_sz)
                 s.ref_dev = torch.empty(segment_sz, dtype=torch.uint8, device=self.device)
+                s.ram_ids = (C.c_uint32 * self.nr_chunks)()
+                s.ram_arg = abi.StromCmd__MemCopySsdToRam()
+                s.ram_arg.dest_uaddr = s.ref_host.data_ptr()
+                s.ram_arg.nr_chunks = self.nr_chunks
+                s.ram_arg.chunk_sz = BLCKSZ
+                s.ram_arg.relseg_sz = 0
+                s.ram_arg.chunk_ids = C.cast(s.ram_ids, C.POINTER(C.c_uint32))
             self.slots.append(s)
 
+    def _alloc_dma_buffer(self, length):
+        """ALLOC_DMA_BUFFER + mmap(MAP_SHARED), as ssd2ram_test does (utils/ssd2ram_test.c:126-147),
+        then page-locked for CUDA so that the H2D of the comparison copy runs at link speed."""
+        arg = abi.StromCmd__AllocDMABuffer()
+        arg.length, arg.node_id = length, -1
+        abi.nvme_strom_ioctl(abi.STROM_IOCTL__ALLOC_DMA_BUFFER, arg)
+        m = mmap.mmap(arg.dmabuf_fdesc, length, mmap.MAP_SHARED, mmap.PROT_READ | mmap.PROT_WRITE)
+        os.close(arg.dmabuf_fdesc)
+        t = torch.frombuffer(m, dtype=torch.uint8)
+        rc = torch.cuda.cudart().cudaHostRegister(t.data_ptr(), length, 0)
+        if int(rc) != 0:
+            raise RuntimeError(f"cudaHostRegister of the DMA buffer failed: {rc}")
+        self._dma_maps.append((m, t))
+        return t
+
     def close(self):
+        for m, t in self._dma_maps:
+            torch.cuda.cudart().cudaHostUnregister(t.data_ptr())
+        self._dma_maps = []
         if self.handle:
             uarg = abi.StromCmd__UnmapGpuMemory()
             uarg.handle = self.handle
@@ -88,35 +119,41 @@ class SegmentPipeline:
         first_page = seg_index * self.nr_chunks
         ids = np.frombuffer(slot.chunk_ids, dtype=np.uint32)
         ids[:] = np.arange(first_page, first_page + self.nr_chunks, dtype=np.uint32)
+        if self.verify or self.via_ram:
+            np.frombuffer(slot.ram_ids, dtype=np.uint32)[:] = ids
         slot.uarg.file_desc = fd
         slot.first_page = first_page
-        abi.nvme_strom_ioctl(abi.STROM_IOCTL__MEMCPY_SSD2GPU, slot.uarg)
-        self.h2d_bytes += self.segment_sz
-        self.counters["nr_ram2gpu"] += slot.uarg.nr_ram2gpu
-        self.counters["nr_ssd2gpu"] += slot.uarg.nr_ssd2gpu
-        self.counters["nr_dma_submit"] += slot.uarg.nr_dma_submit
-        self.counters["nr_dma_blocks"] += slot.uarg.nr_dma_blocks
-        if self.verify:
-            # the reference's own second path: pread through the VFS (:249-252)
-            view = memoryview(slot.ref_host.numpy())
-            done = 0
-            while done < self.segment_sz:
-                n = os.preadv(fd, [view[done:]], first_page * BLCKSZ + done)
-                if n <= 0:
-                    raise IOError("short read on the verification path")
-                done += n
+        if not self.via_ram:
+            abi.nvme_strom_ioctl(abi.STROM_IOCTL__MEMCPY_SSD2GPU, slot.uarg)
+            self.h2d_bytes += self.segment_sz
+            self.counters["nr_ram2gpu"] += slot.uarg.nr_ram2gpu
+            self.counters["nr_ssd2gpu"] += slot.uarg.nr_ssd2gpu
+            self.counters["nr_dma_submit"] += slot.uarg.nr_dma_submit
+            self.counters["nr_dma_blocks"] += slot.uarg.nr_dma_blocks
+        if self.verify or self.via_ram:
+            # the comparison copy takes the other road: MEMCPY_SSD2RAM into a host DMA buffer
+            # (the reference re-reads through the VFS, utils/nvme_test.c:249-252), H2D later
+            slot.ram_arg.file_desc = fd
+            abi.nvme_strom_ioctl(abi.STROM_IOCTL__MEMCPY_SSD2RAM, slot.ram_arg)
         slot.busy = True
 
     def _complete(self, slot):
         warg = abi.StromCmd__MemCopyWait()
-        warg.dma_task_id = slot.uarg.dma_task_id
-        abi.nvme_strom_ioctl(abi.STROM_IOCTL__MEMCPY_WAIT, warg)
+        if not self.via_ram:
+            warg.dma_task_id = slot.uarg.dma_task_id
+            abi.nvme_strom_ioctl(abi.STROM_IOCTL__MEMCPY_WAIT, warg)
+        if self.verify or self.via_ram:
+            warg.dma_task_id = slot.ram_arg.dma_task_id
+            abi.nvme_strom_ioctl(abi.STROM_IOCTL__MEMCPY_WAIT, warg)
         base = self.buffer.data_ptr() + slot.offset
         st = C.c_void_p(self.stream.cuda_stream)
         res = None
         if self.results is not None:
             res = C.c_void_p(self.results.data_ptr() + (slot.first_page - self.results_base) * 8)
         with torch.cuda.stream(self.stream):
+            if self.via_ram:
+                self.buffer[slot.offset:slot.offset + self.segment_sz].copy_(slot.ref_host, non_blocking=True)
+                self.h2d_bytes += self.segment_sz
             if self.verify:
                 slot.ref_dev.copy_(slot.ref_host, non_blocking=True)
                 self.h2d_bytes += self.segment_sz

@@ -9,7 +9,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 VARIANTS = ["tma:8:3", "tma:4:6", "tma:6:4", "tma:12:2", "tma:7:4", "tma:16:1", "tma:8:2", "tma:14:2",
-            "ldg:8:2", "ldg:4:2", "ldg:4:3", "ldg:8:1", "ldg:4:1"]
+            "ldg:8:2", "ldg:4:2", "ldg:4:3", "ldg:8:1", "ldg:4:1", "ldgdyn", "col:12", "col:10", "col:8", "col:6", "col:4"]
 
 
 @pytest.fixture(params=VARIANTS)
