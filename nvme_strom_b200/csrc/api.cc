@@ -225,6 +225,8 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 	unref.armed = false;                                   /* the task owns the ref now */
 	if (want_direct_io())
 		task->fd_direct = open_direct_twin(own_fd);
+	else
+		task->source = source_map_get(own_fd, st);
 	const unsigned long task_id = task->id;
 
 	/* chunks that are mostly in the page cache come back through wb_buffer,
@@ -251,7 +253,7 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 		const bool direct = task->fd_direct >= 0;
 		for (const Piece &p : plan.pieces)
 			jobs.push_back({task, direct ? task->fd_direct : own_fd, direct, p.file_off, p.length,
-							reinterpret_cast<char *>(win->map_address + p.dest_off)});
+							reinterpret_cast<char *>(win->map_address + p.dest_off), task->source.get()});
 		task_add_ref(task, (int)jobs.size());
 		engine_submit(engine_for_window(*win), jobs);
 	}
@@ -323,6 +325,7 @@ static int do_memcpy_ssd2ram(int session, StromCmd__MemCopySsdToRam *arg)
 	if (own_fd < 0)
 		return -errno;
 	DmaTask *task = task_create(session, own_fd, nullptr);
+	task->source = source_map_get(own_fd, st);
 	const unsigned long task_id = task->id;
 	char *base = static_cast<char *>(arg->dest_uaddr) - buf_off;   /* address of buffer offset 0 */
 
@@ -345,7 +348,7 @@ static int do_memcpy_ssd2ram(int session, StromCmd__MemCopySsdToRam *arg)
 		std::vector<Job> jobs;
 		jobs.reserve(plan.pieces.size());
 		for (const Piece &p : plan.pieces)
-			jobs.push_back({task, own_fd, false, p.file_off, p.length, base + p.dest_off});
+			jobs.push_back({task, own_fd, false, p.file_off, p.length, base + p.dest_off, task->source.get()});
 		task_add_ref(task, (int)jobs.size());
 		engine_submit(engine_for_host(), jobs);
 	}

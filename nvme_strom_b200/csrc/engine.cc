@@ -32,6 +32,8 @@
 #include <deque>
 #include <map>
 #include <sched.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
 #include <thread>
 #include <unistd.h>
 
@@ -92,6 +94,73 @@ static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
 		done += (uint32_t)n;
 	}
 	return 0;
+}
+
+/* piece [off, off+len) out of the mapped file; zeros past EOF like read_fully */
+static void copy_from_map(const SourceMap &m, char *dst, uint32_t len, uint64_t off)
+{
+	uint64_t n = off < m.size ? std::min<uint64_t>(len, m.size - off) : 0;
+	if (n)
+		memcpy(dst, m.base + off, n);
+	if (n < len)
+		memset(dst + n, 0, len - n);
+}
+
+static int fetch_piece(const Job &j, char *dst)
+{
+	if (j.src && !j.direct)
+	{
+		copy_from_map(*j.src, dst, j.length, j.file_off);
+		return 0;
+	}
+	return read_fully(j.fd, dst, j.length, j.file_off);
+}
+
+/* ---- cache of mapped source files ---- */
+SourceMap::~SourceMap()
+{
+	if (base)
+		munmap(base, size);
+}
+
+std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st)
+{
+	static int enabled = -1;
+	static std::mutex lock;
+	static std::vector<std::shared_ptr<SourceMap>> cache;
+	if (enabled < 0)
+	{
+		const char *e = getenv("NVME_STROM_SRC");
+		enabled = (e && !strcmp(e, "pread")) ? 0 : 1;
+	}
+	if (!enabled || st.st_size <= 0)
+		return nullptr;
+	std::lock_guard<std::mutex> g(lock);
+	for (size_t i = 0; i < cache.size(); i++)
+	{
+		const SourceMap &m = *cache[i];
+		if (m.dev == (uint64_t)st.st_dev && m.ino == (uint64_t)st.st_ino)
+		{
+			if (m.size == (uint64_t)st.st_size && m.mtime_s == st.st_mtim.tv_sec && m.mtime_ns == st.st_mtim.tv_nsec)
+				return cache[i];
+			cache.erase(cache.begin() + (long)i);      /* file changed: map it afresh */
+			break;
+		}
+	}
+	void *p = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_SHARED, fd, 0);
+	if (p == MAP_FAILED)
+		return nullptr;
+	auto m = std::make_shared<SourceMap>();
+	m->dev = (uint64_t)st.st_dev;
+	m->ino = (uint64_t)st.st_ino;
+	m->size = (uint64_t)st.st_size;
+	m->mtime_s = st.st_mtim.tv_sec;
+	m->mtime_ns = st.st_mtim.tv_nsec;
+	m->base = static_cast<char *>(p);
+	if (cache.size() >= 16)
+		cache.erase(cache.begin());
+	cache.push_back(m);
+	return m;
 }
 
 class Engine {
@@ -169,7 +238,7 @@ private:
 			{
 				const uint64_t t0 = rdtsc_now();
 				stats_dma_started();
-				int rc = read_fully(j.fd, j.dst, j.length, j.file_off);
+				int rc = fetch_piece(j, j.dst);
 				stats_dma_finished(t0);
 				task_put(j.task, rc);
 			}
@@ -218,7 +287,7 @@ private:
 			next = (next + 1) % n_slots;
 			retire(s);                            /* slot's previous copy must be done */
 			const uint64_t t0 = rdtsc_now();
-			int rc = read_fully(j.fd, s.buf, j.length, j.file_off);
+			int rc = fetch_piece(j, s.buf);
 			if (rc == 0)
 			{
 				stats_dma_started();

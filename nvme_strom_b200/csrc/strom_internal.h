@@ -19,6 +19,7 @@
 #include <condition_variable>
 #include <memory>
 #include <mutex>
+#include <sys/stat.h>
 #include <vector>
 
 namespace strom {
@@ -62,6 +63,18 @@ int do_alloc_dma_buffer(StromCmd__AllocDMABuffer *arg);
 int dmabuf_resolve(const void *uaddr, uint64_t *buf_offset, uint64_t *bytes_left,
 				   uint64_t *buf_length);
 
+/* ---- source files mapped for reading ------------------------------------- */
+/* A read-only MAP_SHARED view of the page cache.  Copying out of it costs one
+ * user-space memcpy per piece instead of a pread (no per-page copy_to_user
+ * bookkeeping): +12..44% source rate on the round-1 box, see DESIGN.md 5. */
+struct SourceMap {
+	uint64_t dev = 0, ino = 0, size = 0;
+	long mtime_s = 0, mtime_ns = 0;
+	char *base = nullptr;
+	~SourceMap();
+};
+std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st);   /* null: use pread */
+
 /* ---- asynchronous tasks --------------------------------------------------- */
 struct DmaTask {
 	unsigned long id = 0;
@@ -71,6 +84,7 @@ struct DmaTask {
 	std::atomic<int>  pending{1};         /* 1 (creator) + pieces in flight     */
 	std::atomic<long> status{0};          /* first error wins, :680-686         */
 	std::shared_ptr<GpuWindow> window;    /* null for SSD2RAM                   */
+	std::shared_ptr<SourceMap> source;    /* null: read with pread              */
 	uint64_t      tsc_start = 0;
 };
 DmaTask *task_create(int session, int fd, std::shared_ptr<GpuWindow> win);
@@ -120,6 +134,7 @@ struct Job {
 	uint64_t file_off;
 	uint32_t length;
 	char    *dst;                         /* device or host address              */
+	const SourceMap *src;                 /* kept alive by task->source; may be null */
 };
 class Engine;
 Engine *engine_for_window(const GpuWindow &w);            /* created on demand   */

@@ -32,7 +32,7 @@ class SegmentPipeline:
     """N in-flight segments of ``segment_sz`` bytes landing in one mapped device buffer."""
 
     def __init__(self, device=0, segment_sz=32 << 20, nr_segments=6, verify=False, scan=True,
-                 scan_flags=abi.SCAN_DEFAULT, keep_results=False, via_ram=False):
+                 scan_flags=abi.SCAN_DEFAULT, keep_results=False, via_ram=False, source_only=False):
         """verify: also fetch every segment a second way (MEMCPY_SSD2RAM + H2D) and byte-compare
         the two copies on the GPU.  via_ram: do not use MEMCPY_SSD2GPU at all -- land in a host
         DMA buffer with MEMCPY_SSD2RAM and copy up from there (config C4's comparison arm)."""
@@ -44,7 +44,8 @@ class SegmentPipeline:
         self.nr_segments = nr_segments
         self.nr_chunks = segment_sz // BLCKSZ
         self.verify = verify and not via_ram
-        self.via_ram = via_ram
+        self.via_ram = via_ram or source_only
+        self.source_only = source_only        # file -> pinned host only: the source-rate calibration
         self.scan = scan
         self.scan_flags = scan_flags
         self.keep_results = keep_results
@@ -77,7 +78,7 @@ class SegmentPipeline:
             s.busy = False
             s.first_page = 0
             s.ref_host = s.ref_dev = s.wb = None
-            if verify or via_ram:
+            if verify or self.via_ram:
                 s.ref_host = self._alloc_dma_buffer(segment_sz)
                 s.ref_dev = torch.empty(segment_sz, dtype=torch.uint8, device=self.device)
                 s.ram_ids = (C.c_uint32 * self.nr_chunks)()
@@ -151,6 +152,9 @@ class SegmentPipeline:
         if self.results is not None:
             res = C.c_void_p(self.results.data_ptr() + (slot.first_page - self.results_base) * 8)
         with torch.cuda.stream(self.stream):
+            if self.source_only:
+                slot.event.record(self.stream)
+                return
             if self.via_ram:
                 self.buffer[slot.offset:slot.offset + self.segment_sz].copy_(slot.ref_host, non_blocking=True)
                 self.h2d_bytes += self.segment_sz
