@@ -279,15 +279,19 @@ def run_product(args):
             torch.cuda.synchronize()
             h2d_best = max(h2d_best, (GIB // 2) / (a.elapsed_time(b) * 1e-3) / 1e9)
         del host
-        src_pipe = SegmentPipeline(local_rank, SEG, SLOTS, source_only=True)
-        src_pipe.run(path, first_seg, n_seg)
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(3):
-            src_pipe.run(path, first_seg, n_seg)
-        src_local = (time.perf_counter() - t0) / 3
-        barrier()
-        src_pipe.close()
+        pipe.scan = False
+        lib.strom_debug_skip_h2d(1)                     # same engine, same threads and slots, no H2D
+        try:
+            pipe.run(path, first_seg, n_seg)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(3):
+                pipe.run(path, first_seg, n_seg)
+            src_local = (time.perf_counter() - t0) / 3
+            barrier()
+        finally:
+            lib.strom_debug_skip_h2d(0)
+        pipe.scan = True
         ms_src = max_over_ranks(src_local * 1e3)
 
         def sum_over_ranks(x):
@@ -380,8 +384,8 @@ def run_product(args):
                                   "bound": "h2d" if h2d_total <= source_total else "source",
                                   "peak": round(xfer_roof, 2), "frac": round(e2e / xfer_roof, 4),
                                   "how": "h2d: 512 MiB pinned->device cudaMemcpyAsync per rank, all ranks at once, "
-                                         "best of 4, summed; source: MEMCPY_SSD2RAM of each rank's shard into "
-                                         "page-locked DMA buffers, all ranks at once, same reader threads, no GPU copy"},
+                                         "best of 4, summed; source: the same MEMCPY_SSD2GPU "
+                                         "pipeline with the device copy switched off (strom_debug_skip_h2d), all ranks at once"},
         }
         result.update(extras)
     finally:

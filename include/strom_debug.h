@@ -34,6 +34,12 @@ int strom_plan_chunks_debug(int to_gpu, uint32_t nr_chunks, uint32_t chunk_sz, u
  * physical, length}; returns the number of extents (0 = identity map), or -errno */
 int strom_file_extents_debug(int fd, uint64_t *extents, uint32_t max_extents);
 
+/* Calibration switch: while on, MEMCPY_SSD2GPU pieces are read into the pinned staging
+ * slots by the same reader threads but NOT copied to the device (the window keeps its old
+ * contents).  Measures the source half of the pipeline alone -- the "source read rate" of
+ * the transfer roofline.  Returns the previous setting.  Never leave it on. */
+int strom_debug_skip_h2d(int on);
+
 #ifdef __cplusplus
 }
 #endif

@@ -39,6 +39,8 @@
 
 namespace strom {
 
+static std::atomic<int> g_skip_h2d{0};      /* strom_debug_skip_h2d(): calibration only */
+
 static int env_int(const char *name, int dflt, int lo, int hi)
 {
 	const char *e = getenv(name);
@@ -106,8 +108,24 @@ static void copy_from_map(const SourceMap &m, char *dst, uint32_t len, uint64_t 
 		memset(dst + n, 0, len - n);
 }
 
+/* NVME_STROM_FAULT_EVERY=N: every Nth piece fails with EIO, as a read error on the
+ * device would (the module's completion path, kmod/nvme_strom.c:993-1039, reports the
+ * NVMe status the same way).  Test hook for the error path; off by default. */
+static int injected_fault()
+{
+	static int every = -1;
+	static std::atomic<uint64_t> counter{0};
+	if (every < 0)
+		every = env_int("NVME_STROM_FAULT_EVERY", 0, 0, 1 << 30);
+	if (every == 0)
+		return 0;
+	return (counter.fetch_add(1) + 1) % (uint64_t)every == 0 ? -EIO : 0;
+}
+
 static int fetch_piece(const Job &j, char *dst)
 {
+	if (int rc = injected_fault())
+		return rc;
 	if (j.src && !j.direct)
 	{
 		copy_from_map(*j.src, dst, j.length, j.file_off);
@@ -288,6 +306,11 @@ private:
 			retire(s);                            /* slot's previous copy must be done */
 			const uint64_t t0 = rdtsc_now();
 			int rc = fetch_piece(j, s.buf);
+			if (rc == 0 && g_skip_h2d.load(std::memory_order_relaxed))
+			{
+				task_put(j.task, 0);              /* source-rate calibration: read, do not copy */
+				continue;
+			}
 			if (rc == 0)
 			{
 				stats_dma_started();
@@ -356,3 +379,6 @@ Engine *engine_for_host()
 void engine_submit(Engine *e, const std::vector<Job> &jobs) { e->submit(jobs); }
 
 } /* namespace strom */
+
+#include "strom_debug.h"
+extern "C" int strom_debug_skip_h2d(int on) { return strom::g_skip_h2d.exchange(on ? 1 : 0); }
