@@ -191,6 +191,11 @@ public:
 		int n = host_only ? env_int("NVME_STROM_HOST_READERS", std::min(ncpu, 8), 1, 256) : gpu_reader_count();
 		for (int i = 0; i < n; i++)
 			threads_.emplace_back([this, i] { worker(i); });
+		/* Return only when every worker has its stream, events and pinned slots: page-locked
+		 * allocation synchronises with the device, and must not happen later, while a caller's
+		 * stream callback sits in MEMCPY_WAIT for pieces these workers are to deliver. */
+		std::unique_lock<std::mutex> g(lock_);
+		ready_cv_.wait(g, [&] { return ready_ == n; });
 	}
 	/* engines live until process exit; threads are detached at teardown */
 	~Engine()
@@ -246,11 +251,19 @@ private:
 		s.task = nullptr;
 	}
 
+	void mark_ready()
+	{
+		std::lock_guard<std::mutex> g(lock_);
+		ready_++;
+		ready_cv_.notify_all();
+	}
+
 	void worker(int index)
 	{
 		(void)index;
 		if (host_only_)
 		{
+			mark_ready();
 			Job j;
 			while (pop(&j, true))
 			{
@@ -283,6 +296,7 @@ private:
 			(void)cudaGetLastError();
 			logf(0, "engine(dev=%d): cannot set up staging; failing its jobs", device_);
 		}
+		mark_ready();
 
 		int next = 0;
 		Job j;
@@ -348,6 +362,8 @@ private:
 	std::mutex lock_;
 	std::condition_variable cv_;
 	std::deque<Job> queue_;
+	std::condition_variable ready_cv_;
+	int ready_ = 0;
 	bool stop_ = false;
 	std::vector<std::thread> threads_;
 };

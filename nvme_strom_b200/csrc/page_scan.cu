@@ -554,6 +554,25 @@ static int check_args(const void *pages, const void *ref, bool need_ref, StromSc
 	return 0;
 }
 
+/* With lazy module loading the first launch of a kernel loads it, which synchronises with
+ * the device.  A consumer that parks a stream callback in MEMCPY_WAIT (the reference's
+ * nvme_test does) and then launches would wait on that callback while the engine's copies
+ * wait on the loader: load the default kernels up front instead (called at MAP time). */
+int preload_verify_kernel();
+int preload_kernels()
+{
+	cudaFuncAttributes fa;
+	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, totals_reset_kernel));
+	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, scan_ldg_kernel<8, false, 2, false>));
+	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, scan_ldg_kernel<4, true, 2, false>));
+	DeviceInfo *d = device_info();
+	if (!d)
+		return -1;
+	int n = 0;
+	STROM_CUDA_OR_FAIL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_ldg_kernel<8, false, 2, false>, kLdgThreads, 0));
+	return preload_verify_kernel();
+}
+
 } /* namespace strom */
 
 using namespace strom;

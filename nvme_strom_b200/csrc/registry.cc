@@ -140,6 +140,12 @@ int do_map_gpu_memory(StromCmd__MapGpuMemory *arg)
 		std::lock_guard<std::mutex> g(g_win_lock);
 		g_windows[w->handle] = w;
 	}
+	/* bring the transfer engine of this device/context up now (threads, streams, pinned
+	 * staging), the way the module pins the BAR1 pages at map time: MEMCPY_SSD2GPU then
+	 * never allocates */
+	(void)engine_for_window(*w);
+	if (window_make_current(*w) == 0)
+		(void)preload_kernels();
 	arg->handle = w->handle;
 	arg->gpu_page_sz = (uint32_t)kGpuBoundSize;
 	arg->gpu_npages = (uint32_t)((w->map_length + kGpuBoundSize - 1) >> kGpuBoundShift);

@@ -156,6 +156,8 @@ int stat_info_level();                    /* NVME_STROM_STAT_INFO, default 1    
 void stats_dma_started();
 void stats_dma_finished(uint64_t tsc_start);
 
+int preload_kernels();                   /* page_scan.cu: load the default kernels now */
+
 /* driver-API entry points fetched through the runtime (no link to libcuda) */
 struct DriverApi {
 	int (*cuPointerGetAttribute)(void *data, int attr, unsigned long long ptr) = nullptr;

@@ -10,10 +10,15 @@
  * MEMCPY_SSD2RAM, sends it up, and runs the fused checksum + validation +
  * byte-compare kernel on the two device copies.  -k runs the page scan alone.
  *
- * Like the reference it drives everything from stream callbacks: the slot's
- * stream is held by a host function that sits in MEMCPY_WAIT (legal: WAIT
- * makes no CUDA call), the kernels follow in stream order, a last host
- * function hands the slot back.
+ * Structure: the main thread submits segments (MEMCPY_SSD2GPU, and
+ * MEMCPY_SSD2RAM for -c) as slots free up; a completion thread takes them in
+ * submission order, sits in MEMCPY_WAIT, then queues the upload of the
+ * comparison copy and the kernels on the slot's stream; a stream callback
+ * that only posts a semaphore hands the slot back.  The reference parks a
+ * stream callback in MEMCPY_WAIT instead (utils/nvme_test.c:208-223, :457);
+ * that works with this library too (its own nvme_test runs on it), but a
+ * blocked callback ahead of queued H2D copies can starve other streams that
+ * share a hardware queue with it, so the wait lives on a plain thread here.
  */
 #include <cerrno>
 #include <cstdint>
@@ -81,21 +86,28 @@ struct Slot {
 	int file_desc;
 };
 
-static void CUDART_CB cb_dma_wait(void *priv)
+static int debug_trace = 0;
+#define TRACE(...) do { if (debug_trace) { fprintf(stderr, __VA_ARGS__); fputc('\n', stderr); } } while (0)
+
+static void wait_for_segment(Slot *s)
 {
-	Slot *s = static_cast<Slot *>(priv);
 	StromCmd__MemCopyWait w;
 
 	memset(&w, 0, sizeof(w));
 	w.dma_task_id = s->uarg.dma_task_id;
+	TRACE("slot %d: wait gpu task %lu", s->index, w.dma_task_id);
 	int rv = nvme_strom_ioctl(STROM_IOCTL__MEMCPY_WAIT, &w);
 	if (w.status)
+	{
 		printf("async dma (id=%lu, status=%ld)\n", w.dma_task_id, w.status);
+		fflush(stdout);
+	}
 	SYS_OK(rv == 0, "STROM_IOCTL__MEMCPY_WAIT");
 	if (enable_checks)
 	{
 		w.dma_task_id = s->rarg.dma_task_id;
 		rv = nvme_strom_ioctl(STROM_IOCTL__MEMCPY_WAIT, &w);
+		TRACE("slot %d: ram task %lu done rv=%d", s->index, w.dma_task_id, rv);
 		SYS_OK(rv == 0, "STROM_IOCTL__MEMCPY_WAIT (comparison copy)");
 	}
 }
@@ -104,6 +116,7 @@ static void CUDART_CB cb_release(void *priv)
 {
 	Slot *s = static_cast<Slot *>(priv);
 
+	TRACE("slot %d: release", s->index);
 	pthread_mutex_lock(&buffer_lock);
 	s->is_running = 0;
 	pthread_mutex_unlock(&buffer_lock);
@@ -314,13 +327,57 @@ static void launch_checks(Slot *s)
 	}
 }
 
+/* submission-ordered hand-over from the main thread to the completion thread */
+static std::vector<Slot *> ready_fifo;
+static size_t fifo_head = 0;
+static bool fifo_closed = false;
+static pthread_mutex_t fifo_lock = PTHREAD_MUTEX_INITIALIZER;
+static pthread_cond_t fifo_cond = PTHREAD_COND_INITIALIZER;
+static void launch_checks(Slot *s);
+
+static void fifo_push(Slot *s)
+{
+	pthread_mutex_lock(&fifo_lock);
+	if (s)
+		ready_fifo.push_back(s);
+	else
+		fifo_closed = true;
+	pthread_cond_signal(&fifo_cond);
+	pthread_mutex_unlock(&fifo_lock);
+}
+
+static void *completion_thread(void *)
+{
+	CUDA_OK(cudaSetDevice(device_index));
+	for (;;)
+	{
+		pthread_mutex_lock(&fifo_lock);
+		while (fifo_head == ready_fifo.size() && !fifo_closed)
+			pthread_cond_wait(&fifo_cond, &fifo_lock);
+		if (fifo_head == ready_fifo.size())
+		{
+			pthread_mutex_unlock(&fifo_lock);
+			break;
+		}
+		Slot *s = ready_fifo[fifo_head++];
+		pthread_mutex_unlock(&fifo_lock);
+		wait_for_segment(s);
+		launch_checks(s);
+		CUDA_OK(cudaLaunchHostFunc(s->stream, cb_release, s));
+	}
+	return NULL;
+}
+
 static void exec_test_by_strom(unsigned long handle, int fdesc, size_t file_size)
 {
 	std::vector<Slot> slots;
 	struct timeval tv1, tv2;
 	long usec_sem_wait = 0, nr_ram2gpu = 0, nr_ssd2gpu = 0, nr_dma_submit = 0, nr_dma_blocks = 0;
 
+	pthread_t completer;
+
 	setup_slots(slots, fdesc, handle);
+	SYS_OK(pthread_create(&completer, NULL, completion_thread, NULL) == 0, "pthread_create");
 	gettimeofday(&tv1, NULL);
 	for (size_t fpos = 0; fpos < file_size; fpos += segment_sz)
 	{
@@ -335,10 +392,11 @@ static void exec_test_by_strom(unsigned long handle, int fdesc, size_t file_size
 		nr_dma_blocks += s->uarg.nr_dma_blocks;
 		if (enable_checks)
 			SYS_OK(nvme_strom_ioctl(STROM_IOCTL__MEMCPY_SSD2RAM, &s->rarg) == 0, "STROM_IOCTL__MEMCPY_SSD2RAM");
-		CUDA_OK(cudaLaunchHostFunc(s->stream, cb_dma_wait, s));
-		launch_checks(s);
-		CUDA_OK(cudaLaunchHostFunc(s->stream, cb_release, s));
+		TRACE("slot %d: submitted fpos=%zu", s->index, fpos);
+		fifo_push(s);
 	}
+	fifo_push(NULL);
+	pthread_join(completer, NULL);
 	drain(slots, &usec_sem_wait);
 	gettimeofday(&tv2, NULL);
 	show_throughput(file_size, tv1, tv2, usec_sem_wait, nr_ram2gpu, nr_ssd2gpu, nr_dma_submit, nr_dma_blocks);
@@ -444,6 +502,8 @@ int main(int argc, char *argv[])
 	int c, fdesc;
 	struct stat stbuf;
 
+	debug_trace = getenv("STROM_TEST_TRACE") != NULL;
+	setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);     /* slot streams + engine streams: avoid queue sharing */
 	while ((c = getopt(argc, argv, "d:n:s:ckpf::h")) >= 0)
 	{
 		switch (c)

@@ -60,6 +60,13 @@ verify_blocks_kernel(const uint4 *a, const uint4 *b, const uint32_t *map, uint64
 	flush_totals(acc, lane == 0, s_tot, totals);
 }
 
+int preload_verify_kernel()
+{
+	cudaFuncAttributes fa;
+	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, verify_blocks_kernel));
+	return 0;
+}
+
 } /* namespace strom */
 
 using namespace strom;

@@ -59,5 +59,5 @@ def test_mapping_dump_and_usage(c5_file):
 def test_read_error_is_reported(c5_file):
     r = subprocess.run([TOOL, "-d", "0", c5_file], capture_output=True, text=True, timeout=300,
                        env=dict(os.environ, NVME_STROM_FAULT_EVERY="50"))
-    assert r.returncode == 1
-    assert "async dma" in r.stdout and "MEMCPY_WAIT" in r.stderr
+    assert r.returncode == 1, r.stdout + r.stderr
+    assert "MEMCPY_WAIT" in r.stderr and "Input/output error" in r.stderr, r.stdout + r.stderr
