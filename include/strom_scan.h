@@ -96,6 +96,22 @@ int strom_scan_verify_pages_dev(const void *d_pages, const void *d_ref, uint64_t
 								StromPageResult *d_results, StromScanTotals *d_totals,
 								void *stream);
 
+/* the step after validation: emit (blkno, lineoff, lp_off, lp_len) of every LP_NORMAL
+ * line pointer, page after page, lineoff ascending -- the tuple stream that
+ * nvmestrom_next_tuple walks on the CPU (pgsql/nvme_strom.c:1054-1092).  Applies
+ * PostgreSQL's macros' view (PageGetMaxOffsetNumber, ItemIdIsNormal), no validity rule.
+ *   d_page_offsets  out, n_pages + 1 entries: items of page i are
+ *                   d_items[d_page_offsets[i] .. d_page_offsets[i+1])
+ *   d_item_count    out (may be NULL): total number of items
+ *   d_items         out, at most max_items stored (the count is still exact) */
+typedef struct StromItem {
+	uint32_t blkno;
+	uint16_t lineoff, lp_off, lp_len, pad;
+} StromItem;
+int strom_extract_items_dev(const void *d_pages, uint64_t n_pages, uint32_t first_blkno,
+							StromItem *d_items, uint64_t max_items,
+							uint64_t *d_page_offsets, uint64_t *d_item_count, void *stream);
+
 /* ---- handle level: windows of MAP_GPU_MEMORY, HOST outputs, synchronous --- */
 
 int strom_scan_pages(unsigned long handle, size_t offset, uint64_t n_pages,

@@ -133,6 +133,13 @@ lib.strom_scan_pages.argtypes = [C.c_ulong, C.c_size_t, C.c_uint64, C.c_uint32, 
                                  C.c_void_p, C.c_void_p]
 lib.strom_verify_pages.argtypes = [C.c_ulong, C.c_size_t, C.c_ulong, C.c_size_t, C.c_uint64,
                                    C.c_void_p, C.c_void_p]
+class StromItem(C.Structure):
+    _fields_ = [("blkno", C.c_uint32), ("lineoff", C.c_uint16), ("lp_off", C.c_uint16), ("lp_len", C.c_uint16),
+                ("pad", C.c_uint16)]
+
+
+lib.strom_extract_items_dev.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p,
+                                        C.c_void_p, C.c_void_p]
 STATIC_SCRATCH_MAX_PAGES = 131072
 lib.strom_scan_pages_static.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
 lib.strom_partition_segments.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32,
