@@ -59,6 +59,7 @@ class SegmentPipeline:
         abi.nvme_strom_ioctl(abi.STROM_IOCTL__MAP_GPU_MEMORY, marg)
         self.handle = marg.handle
         self.h2d_bytes = 0
+        self._fds, self._relseg = [], 0
         self.slots = []
         self._dma_maps = []
         for i in range(nr_segments):
@@ -78,6 +79,7 @@ class SegmentPipeline:
             s.busy = False
             s.first_page = 0
             s.ref_host = s.ref_dev = s.wb = None
+            s.ram_ids = s.ram_arg = None
             if verify or self.via_ram:
                 s.ref_host = self._alloc_dma_buffer(segment_sz)
                 s.ref_dev = torch.empty(segment_sz, dtype=torch.uint8, device=self.device)
@@ -118,6 +120,8 @@ class SegmentPipeline:
     # -- one segment ---------------------------------------------------------
     def _submit(self, slot, fd, seg_index):
         first_page = seg_index * self.nr_chunks
+        if self._relseg:
+            fd = self._fds[first_page // self._relseg]
         ids = np.frombuffer(slot.chunk_ids, dtype=np.uint32)
         ids[:] = np.arange(first_page, first_page + self.nr_chunks, dtype=np.uint32)
         if self.verify or self.via_ram:
@@ -172,20 +176,38 @@ class SegmentPipeline:
             slot.event.record(self.stream)
 
     # -- whole range ------------------------------------------------------------
-    def run(self, path, first_segment=0, n_segments=None):
-        """Loads segments [first_segment, first_segment + n_segments) of ``path``
-        and processes them on the GPU.  Returns (totals list, counters dict)."""
-        fd = os.open(path, os.O_RDONLY)
+    def run(self, path, first_segment=0, n_segments=None, relseg_sz=0):
+        """Loads segments [first_segment, first_segment + n_segments) and processes them on the
+        GPU.  Returns (totals list, counters dict).
+
+        ``path`` is one file, or -- with ``relseg_sz`` > 0 -- the list of segment files of one
+        relation, each holding ``relseg_sz`` blocks (PostgreSQL: RELSEG_SIZE = 131072 blocks = 1 GB;
+        block b lives in file b // relseg_sz at chunk b % relseg_sz, which is what the ioctl's
+        relseg_sz does: kmod/nvme_strom.c:1524-1527; one fd per file as pgsql/nvme_strom.c:952-959).
+        Block numbers, and with them the page checksums, stay relation-wide."""
+        paths = [path] if isinstance(path, str) else list(path)
+        if len(paths) > 1 and relseg_sz <= 0:
+            raise ValueError("several files need relseg_sz")
+        if relseg_sz and relseg_sz % self.nr_chunks:
+            raise ValueError("a pipeline segment must not straddle two relation files")
+        fds = [os.open(p, os.O_RDONLY) for p in paths]
+        fd = fds[0]
         try:
             carg = abi.StromCmd__CheckFile()
-            carg.fdesc = fd
-            abi.nvme_strom_ioctl(abi.STROM_IOCTL__CHECK_FILE, carg)
-            fsize = os.fstat(fd).st_size
-            total = fsize // self.segment_sz                  # the tail is dropped, :785
+            total = 0
+            for f in fds:
+                carg.fdesc = f
+                abi.nvme_strom_ioctl(abi.STROM_IOCTL__CHECK_FILE, carg)
+                total += os.fstat(f).st_size // self.segment_sz   # the tail is dropped, :785
             if n_segments is None:
                 n_segments = total - first_segment
             if first_segment + n_segments > total:
                 raise ValueError("segment range runs past the end of the file")
+            self._fds, self._relseg = fds, relseg_sz
+            for s_ in self.slots:
+                s_.uarg.relseg_sz = relseg_sz
+                if s_.ram_arg is not None:
+                    s_.ram_arg.relseg_sz = relseg_sz
             self.counters = dict(nr_ram2gpu=0, nr_ssd2gpu=0, nr_dma_submit=0, nr_dma_blocks=0)
             self.h2d_bytes = 0
             if self.keep_results:
@@ -214,7 +236,8 @@ class SegmentPipeline:
             return out, dict(self.counters, h2d_bytes=self.h2d_bytes, d2h_bytes=abi.T_COUNT * 8,
                              n_segments=n_segments)
         finally:
-            os.close(fd)
+            for f in fds:
+                os.close(f)
 
     def results_host(self):
         """per-page records (n, 4) uint16: checksum, flags, n_normal, n_bad_lp"""
