@@ -80,35 +80,21 @@ static int do_check_file(StromCmd__CheckFile *arg)
 /* ------------------------------------------------------------------ */
 /* MEMCPY_SSD2GPU / MEMCPY_SSD2RAM                                     */
 /* ------------------------------------------------------------------ */
+/* switches are read once, on first use (thread-safe function-local statics) */
 static bool want_cache_split()
 {
-	static int v = -1;
-	if (v < 0)
-	{
-		const char *e = getenv("NVME_STROM_PGCACHE_SPLIT");
-		v = (e && atoi(e) != 0) ? 1 : 0;
-	}
-	return v == 1;
+	static const bool v = [] { const char *e = getenv("NVME_STROM_PGCACHE_SPLIT"); return e && atoi(e) != 0; }();
+	return v;
 }
 static bool want_fiemap()
 {
-	static int v = -1;
-	if (v < 0)
-	{
-		const char *e = getenv("NVME_STROM_FIEMAP");
-		v = (e && atoi(e) == 0) ? 0 : 1;
-	}
-	return v == 1;
+	static const bool v = [] { const char *e = getenv("NVME_STROM_FIEMAP"); return !(e && atoi(e) == 0); }();
+	return v;
 }
 static bool want_direct_io()
 {
-	static int v = -1;
-	if (v < 0)
-	{
-		const char *e = getenv("NVME_STROM_IO");
-		v = (e && !strcmp(e, "direct")) ? 1 : 0;
-	}
-	return v == 1;
+	static const bool v = [] { const char *e = getenv("NVME_STROM_IO"); return e && !strcmp(e, "direct"); }();
+	return v;
 }
 
 /* extent maps are cached per open file description identity */

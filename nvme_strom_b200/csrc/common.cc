@@ -34,12 +34,7 @@ bool cuda_failed(cudaError_t rc, const char *what)
 
 int verbose_level()
 {
-	static int level = -1;
-	if (level < 0)
-	{
-		const char *s = getenv("NVME_STROM_VERBOSE");
-		level = s ? atoi(s) : 0;
-	}
+	static const int level = [] { const char *s = getenv("NVME_STROM_VERBOSE"); return s ? atoi(s) : 0; }();
 	return level;
 }
 

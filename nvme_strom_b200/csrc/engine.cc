@@ -66,12 +66,13 @@ static int gpu_reader_count()
  * but not below 256KB, where the per-copy cost of the DMA engine starts to show. */
 uint32_t engine_piece_for(uint64_t request_bytes)
 {
+	static const int div = env_int("NVME_STROM_PIECE_DIV", 0, 0, 64);   /* 0: one piece per reader */
 	const uint32_t cap = engine_piece_max();
-	uint64_t per_reader = request_bytes / (uint64_t)gpu_reader_count();
-	per_reader &= ~(uint64_t)(128 * 1024 - 1);
-	if (per_reader >= cap)
+	uint64_t per = request_bytes / (uint64_t)(div > 0 ? div : gpu_reader_count());
+	per &= ~(uint64_t)(128 * 1024 - 1);
+	if (per >= cap)
 		return cap;
-	return (uint32_t)std::max<uint64_t>(per_reader, 256 * 1024);
+	return (uint32_t)std::max<uint64_t>(per, 256 * 1024);
 }
 
 static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
@@ -113,10 +114,8 @@ static void copy_from_map(const SourceMap &m, char *dst, uint32_t len, uint64_t 
  * NVMe status the same way).  Test hook for the error path; off by default. */
 static int injected_fault()
 {
-	static int every = -1;
+	static const int every = env_int("NVME_STROM_FAULT_EVERY", 0, 0, 1 << 30);
 	static std::atomic<uint64_t> counter{0};
-	if (every < 0)
-		every = env_int("NVME_STROM_FAULT_EVERY", 0, 0, 1 << 30);
 	if (every == 0)
 		return 0;
 	return (counter.fetch_add(1) + 1) % (uint64_t)every == 0 ? -EIO : 0;
@@ -143,14 +142,9 @@ SourceMap::~SourceMap()
 
 std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st)
 {
-	static int enabled = -1;
+	static const bool enabled = [] { const char *e = getenv("NVME_STROM_SRC"); return !(e && !strcmp(e, "pread")); }();
 	static std::mutex lock;
 	static std::vector<std::shared_ptr<SourceMap>> cache;
-	if (enabled < 0)
-	{
-		const char *e = getenv("NVME_STROM_SRC");
-		enabled = (e && !strcmp(e, "pread")) ? 0 : 1;
-	}
 	if (!enabled || st.st_size <= 0)
 		return nullptr;
 	std::lock_guard<std::mutex> g(lock);
@@ -281,13 +275,16 @@ private:
 		const bool bound = (ctx_ && api.ok && api.cuCtxSetCurrent(ctx_) == 0) ||
 					   cudaSetDevice(device_) == cudaSuccess;
 		const int n_slots = env_int("NVME_STROM_SLOTS", 2, 2, 16);
+		/* staging is only ever written by the CPU and read by the DMA engine: write-combined
+		 * memory keeps it out of the caches (NVME_STROM_WC=1; off by default) */
+		const unsigned wc_flag = env_int("NVME_STROM_WC", 0, 0, 1) ? cudaHostAllocWriteCombined : 0;
 		const uint32_t slot_sz = engine_piece_max();
 		std::vector<Slot> slots((size_t)n_slots);
 		cudaStream_t stream = nullptr;
 		bool ready = bound && cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking) == cudaSuccess;
 		for (int i = 0; ready && i < n_slots; i++)
 		{
-			if (cudaHostAlloc((void **)&slots[i].buf, slot_sz, cudaHostAllocPortable) != cudaSuccess ||
+			if (cudaHostAlloc((void **)&slots[i].buf, slot_sz, cudaHostAllocPortable | wc_flag) != cudaSuccess ||
 				cudaEventCreateWithFlags(&slots[i].ev, cudaEventDisableTiming) != cudaSuccess)
 				ready = false;
 		}

@@ -492,12 +492,7 @@ Stats g_stats;
 
 int stat_info_level()
 {
-	static int level = -1;
-	if (level < 0)
-	{
-		const char *e = getenv("NVME_STROM_STAT_INFO");
-		level = e ? atoi(e) : 1;
-	}
+	static const int level = [] { const char *e = getenv("NVME_STROM_STAT_INFO"); return e ? atoi(e) : 1; }();
 	return level;
 }
 

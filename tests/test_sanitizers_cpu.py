@@ -1,0 +1,33 @@
+"""The host pipeline under ThreadSanitizer and AddressSanitizer+UBSan: a native driver
+(tests/native/host_pipeline_san.cc) runs 6 threads x 8 in-flight MEMCPY_SSD2RAM tasks over
+the task table, the DMA-buffer registry, the engines and the planner.  The reference has no
+race detection."""
+import os
+import subprocess
+
+import pytest
+
+from conftest import ROOT
+
+CSRC = os.path.join(ROOT, "nvme_strom_b200", "csrc")
+HOST_SOURCES = ["common.cc", "heapgen.cc", "hostutil.cc", "registry.cc", "planner.cc", "engine.cc", "api.cc"]
+CUDA = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+
+
+@pytest.mark.parametrize("san", ["thread", "address,undefined"])
+def test_host_pipeline_under_sanitizer(tmp_path, san):
+    exe = str(tmp_path / "host_san")
+    cmd = ["g++", "-std=c++17", "-O1", "-g", f"-fsanitize={san}", "-fno-omit-frame-pointer", "-pthread",
+           "-I", os.path.join(ROOT, "include"), "-I", CSRC, "-I", os.path.join(CUDA, "include"),
+           os.path.join(ROOT, "tests", "native", "host_pipeline_san.cc")] + \
+          [os.path.join(CSRC, f) for f in HOST_SOURCES] + \
+          ["-L", os.path.join(CUDA, "lib64"), "-lcudart", "-ldl", "-lrt", "-o", exe]
+    subprocess.check_call(cmd)
+    env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(CUDA, "lib64") + ":" + os.environ.get("LD_LIBRARY_PATH", ""),
+               TSAN_OPTIONS="halt_on_error=1 second_deadlock_stack=1", ASAN_OPTIONS="detect_leaks=0",
+               UBSAN_OPTIONS="halt_on_error=1")
+    r = subprocess.run([exe, str(tmp_path / "san.heap")], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-6000:]
+    assert "host pipeline ok" in r.stdout
+    assert "WARNING: ThreadSanitizer" not in r.stderr and "ERROR: AddressSanitizer" not in r.stderr
+    assert "runtime error" not in r.stderr

@@ -91,8 +91,8 @@ def main():
     del view, host
 
     # 3. the pipeline
-    for readers, slot_kb, slots in [(8, 4096, 2), (12, 4096, 2), (14, 4096, 2), (16, 4096, 2), (16, 4096, 3),
-                                    (16, 8192, 2), (12, 8192, 2), (16, 16384, 2), (20, 4096, 2)]:
+    for readers, slot_kb, slots in [(6, 4096, 2), (8, 4096, 2), (10, 4096, 2), (12, 4096, 2), (8, 4096, 3),
+                                    (10, 2048, 3), (8, 2048, 3), (12, 2048, 2)]:
         if readers > 2 * (os.cpu_count() or 1):
             continue
         env = dict(os.environ, NVME_STROM_READERS=str(readers), NVME_STROM_SLOT_KB=str(slot_kb),
