@@ -375,7 +375,7 @@ def run_product(args):
                     "h2d_bytes_per_step": int(counters["h2d_bytes"]) * world,
                     "d2h_bytes_per_step": int(counters["d2h_bytes"]) * world},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "scan_ldg_kernel<8,false,2>", "achieved": round(achieved, 1),
+            "roofline": {"bound": "hbm", "kernel": "scan_ring_kernel<512,16>", "achieved": round(achieved, 1),
                          "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                          "algorithmic_bytes_per_launch": pages_mine * 8192},

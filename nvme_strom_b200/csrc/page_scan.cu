@@ -336,6 +336,490 @@ scan_ldg_kernel(ScanArgs a)
 }
 
 /* ------------------------------------------------------------------ */
+/* kernel 2b: kernel 2 with a small instruction footprint.  Kernel 2      */
+/* unrolls all 64 rows with the line-pointer checks inlined in each: 166KB */
+/* of SASS, and ncu shows warps waiting for instructions as often as for  */
+/* memory (stall "no instruction" 3.4 vs "long scoreboard" 3.3 per issue). */
+/* Here only two batches (ping-pong register buffers) are unrolled and the */
+/* line-pointer rules live in one out-of-line function that the few rows   */
+/* holding line pointers call.                                             */
+/* ------------------------------------------------------------------ */
+__device__ __noinline__ uint32_t lp_check_row(uint32_t x, uint32_t y, uint32_t z, uint32_t w, uint32_t widx,
+											  uint32_t upper, uint32_t special, uint32_t nlp)
+{
+	PageHeader h;
+	h.upper = upper;
+	h.special = special;
+	h.nlp = nlp;
+	const uint32_t lp_end = kHdrWords + nlp;
+	uint32_t cnt = 0;
+	if (widx + 0 >= kHdrWords && widx + 0 < lp_end) cnt += lp_check(x, h);
+	if (widx + 1 >= kHdrWords && widx + 1 < lp_end) cnt += lp_check(y, h);
+	if (widx + 2 >= kHdrWords && widx + 2 < lp_end) cnt += lp_check(z, h);
+	if (widx + 3 >= kHdrWords && widx + 3 < lp_end) cnt += lp_check(w, h);
+	return cnt;
+}
+
+/* the per-page bookkeeping that must survive the 64 rows, squeezed into two registers */
+__device__ __forceinline__ uint32_t pack_header_state(const PageHeader &h)
+{
+	return h.stored_checksum | (h.is_new ? 0x10000u : 0u) | (h.sane ? 0x20000u : 0u) | (h.lp_hdr_bad ? 0x40000u : 0u);
+}
+__device__ __forceinline__ PageHeader unpack_header_state(uint32_t st)
+{
+	PageHeader h = {};
+	h.stored_checksum = st & 0xFFFFu;
+	h.is_new = (st & 0x10000u) != 0;
+	h.sane = (st & 0x20000u) != 0;
+	h.lp_hdr_bad = (st & 0x40000u) != 0;
+	return h;
+}
+
+/* one finished page straight into the block's shared counters (k == 0 lanes only): keeps the
+ * 17 registers of a per-thread TotalsAcc out of the streaming loop */
+__device__ __forceinline__ void
+tally_page(unsigned long long *s_tot, const StromPageResult &r, uint32_t first_unit, uint64_t byte_base)
+{
+	atomicAdd(&s_tot[STROM_T_PAGES], 1ull);
+	atomicAdd(&s_tot[STROM_T_N_NORMAL], (unsigned long long)r.n_normal);
+	atomicXor(&s_tot[STROM_T_XOR_CHECKSUM], (unsigned long long)r.checksum);
+	atomicAdd(&s_tot[STROM_T_SUM_CHECKSUM], (unsigned long long)r.checksum);
+	if (r.flags)
+	{
+		if (r.flags & STROM_PF_ZERO)          atomicAdd(&s_tot[STROM_T_ZERO], 1ull);
+		if (r.flags & STROM_PF_NEW)           atomicAdd(&s_tot[STROM_T_NEW], 1ull);
+		if (r.flags & STROM_PF_CHECKSUM_FAIL) atomicAdd(&s_tot[STROM_T_CHECKSUM_FAIL], 1ull);
+		if (r.flags & STROM_PF_HEADER_INSANE) atomicAdd(&s_tot[STROM_T_HEADER_FAIL], 1ull);
+		if (r.flags & STROM_PF_LP_BAD)        atomicAdd(&s_tot[STROM_T_LP_BAD_PAGES], 1ull);
+		if (r.flags & STROM_PF_INVALID)       atomicAdd(&s_tot[STROM_T_INVALID], 1ull);
+	}
+	if (r.n_bad_lp)
+		atomicAdd(&s_tot[STROM_T_N_BAD_LP], (unsigned long long)r.n_bad_lp);
+	if (first_unit != 0xFFFFu)
+	{
+		atomicAdd(&s_tot[STROM_T_MISMATCH_BLOCKS], 1ull);
+		atomicMin(&s_tot[STROM_T_FIRST_MISMATCH], (unsigned long long)(byte_base + first_unit * 16));
+	}
+}
+
+__device__ __forceinline__ void publish_totals(const unsigned long long *s_tot, unsigned long long *g_tot)
+{
+	__syncthreads();
+	if (threadIdx.x < STROM_T_COUNT)
+	{
+		const unsigned long long v = s_tot[threadIdx.x];
+		if (threadIdx.x == STROM_T_FIRST_MISMATCH)
+		{
+			if (v != ~0ull) atomicMin(&g_tot[threadIdx.x], v);
+		}
+		else if (threadIdx.x == STROM_T_XOR_CHECKSUM)
+		{
+			if (v) atomicXor(&g_tot[threadIdx.x], v);
+		}
+		else if (v)
+			atomicAdd(&g_tot[threadIdx.x], v);
+	}
+}
+
+template <int R, bool VERIFY, int MINB, int THREADS = kLdgThreads>
+__global__ void __launch_bounds__(THREADS, MINB)
+scan_lean_kernel(ScanArgs a)
+{
+	__shared__ unsigned long long s_tot[STROM_T_COUNT];
+	constexpr int NB = 64 / R;
+	static_assert(NB % 2 == 0, "two batches per loop trip");
+	constexpr uint32_t FULL = 0xFFFFFFFFu;
+	constexpr int RV = VERIFY ? R : 1;
+	const uint32_t lane = threadIdx.x & 31, k = lane & 7, gbase = lane & ~7u;
+	/* page numbers fit 32 bits (the launcher refuses more than 2^32 pages = 32 TiB) */
+	const uint32_t n_pages = (uint32_t)a.n_pages;
+	const uint32_t n_groups = (gridDim.x * THREADS) >> 3;
+	uint32_t page = (blockIdx.x * THREADS + threadIdx.x) >> 3;
+	const uint32_t seed0 = kLaneSeed[4 * k], seed1 = kLaneSeed[4 * k + 1],
+				   seed2 = kLaneSeed[4 * k + 2], seed3 = kLaneSeed[4 * k + 3];
+
+	if (threadIdx.x < STROM_T_COUNT)
+		s_tot[threadIdx.x] = (threadIdx.x == STROM_T_FIRST_MISMATCH) ? ~0ull : 0ull;
+	__syncthreads();
+
+	if (page - (lane >> 3) < n_pages)
+	{
+		auto row_ptr = [&](const uint4 *base, uint32_t pg) {
+			return base + (size_t)(pg < n_pages ? pg : n_pages - 1) * 512 + k;
+		};
+		const uint4 *p = row_ptr(a.pages, page);
+		const uint4 *q = VERIFY ? row_ptr(a.ref, page) : nullptr;
+		uint4 bufa[R], bufb[R], refa[RV], refb[RV];
+
+#pragma unroll
+		for (int r = 0; r < R; r++)
+		{
+			bufa[r] = ldg_stream(p + r * 8);
+			if (VERIFY) refa[r] = ldg_stream(q + r * 8);
+		}
+		for (;;)
+		{
+			/* 64-bit overflow-free: n_groups <= 2^20, pages < 2^32 - 2^21 is checked at launch */
+			const uint32_t npage = page + n_groups;
+			const bool more = npage - (lane >> 3) < n_pages;
+			uint32_t s0 = seed0, s1 = seed1, s2 = seed2, s3 = seed3;
+			uint32_t orv = 0, cnt = 0, first_unit = 0xFFFFu;
+			uint32_t hstate = 0, bounds = 0, lp_end = 0;        /* bounds = pd_upper | pd_special << 16 */
+
+			auto compute = [&](const uint4 (&x)[R], const uint4 (&y)[RV], int b, bool first_batch) {
+#pragma unroll
+				for (int r = 0; r < R; r++)
+				{
+					const uint32_t row = (uint32_t)b * R + r;
+					uint4 v = x[r];
+					if (r == 0 && first_batch)
+					{
+						const uint32_t w2 = __shfl_sync(FULL, v.z, gbase);
+						const uint32_t w3 = __shfl_sync(FULL, v.w, gbase);
+						const uint32_t w4 = __shfl_sync(FULL, v.x, gbase + 1);
+						const PageHeader h = decode_header(w2, w3, w4);
+						hstate = pack_header_state(h);
+						bounds = h.upper | (h.special << 16);
+						lp_end = kHdrWords + h.nlp;
+					}
+					orv |= v.x | v.y | v.z | v.w;
+					if (VERIFY)
+					{
+						const uint4 u = y[r];
+						if (((v.x ^ u.x) | (v.y ^ u.y) | (v.z ^ u.z) | (v.w ^ u.w)) != 0)
+							first_unit = min(first_unit, row * 8 + k);
+					}
+					if (row * 32 < lp_end)
+						cnt += lp_check_row(v.x, v.y, v.z, v.w, row * 32 + 4 * k, bounds & 0xFFFFu, bounds >> 16,
+											lp_end - kHdrWords);
+					if (r == 0 && first_batch && k == 0)
+						v.z &= 0xFFFF0000u;
+					s0 = fnv_mix(s0, v.x);
+					s1 = fnv_mix(s1, v.y);
+					s2 = fnv_mix(s2, v.z);
+					s3 = fnv_mix(s3, v.w);
+				}
+			};
+
+#pragma unroll 1
+			for (int b = 0; b < NB; b += 2)
+			{
+#pragma unroll
+				for (int r = 0; r < R; r++)                              /* batch b+1 -> B */
+				{
+					bufb[r] = ldg_stream(p + ((b + 1) * R + r) * 8);
+					if (VERIFY) refb[r] = ldg_stream(q + ((b + 1) * R + r) * 8);
+				}
+				compute(bufa, refa, b, b == 0);
+				const bool last = (b + 2 >= NB);
+				if (!last || more)                                        /* batch b+2, or the next page -> A */
+				{
+					const uint4 *src = last ? row_ptr(a.pages, npage) : p + (b + 2) * R * 8;
+					const uint4 *rsrc = VERIFY ? (last ? row_ptr(a.ref, npage) : q + (b + 2) * R * 8) : nullptr;
+#pragma unroll
+					for (int r = 0; r < R; r++)
+					{
+						bufa[r] = ldg_stream(src + r * 8);
+						if (VERIFY) refa[r] = ldg_stream(rsrc + r * 8);
+					}
+				}
+				compute(bufb, refb, b + 1, false);
+			}
+			uint32_t hash = fnv_mix(fnv_mix(s0, 0), 0) ^ fnv_mix(fnv_mix(s1, 0), 0) ^
+							fnv_mix(fnv_mix(s2, 0), 0) ^ fnv_mix(fnv_mix(s3, 0), 0);
+#pragma unroll
+			for (int d = 4; d >= 1; d >>= 1)
+			{
+				hash ^= __shfl_xor_sync(FULL, hash, d);
+				orv |= __shfl_xor_sync(FULL, orv, d);
+				cnt += __shfl_xor_sync(FULL, cnt, d);
+				if (VERIFY) first_unit = min(first_unit, __shfl_xor_sync(FULL, first_unit, d));
+			}
+			if (k == 0 && page < n_pages)
+			{
+				const StromPageResult r = finish_page(hash, a.first_blkno + page, orv == 0, unpack_header_state(hstate), cnt);
+				if (a.results)
+					a.results[page] = r;
+				tally_page(s_tot, r, VERIFY ? first_unit : 0xFFFFu, a.base_offset + (uint64_t)page * STROM_BLCKSZ);
+			}
+			if (!more)
+				break;
+			page = npage;
+			p = row_ptr(a.pages, page);
+			if (VERIFY) q = row_ptr(a.ref, page);
+		}
+	}
+	publish_totals(s_tot, a.totals);
+}
+
+/* ------------------------------------------------------------------ */
+/* kernel 2c: rolling register window.  Same mapping and helpers as 2b,   */
+/* but instead of two batch buffers that alternate (rows in flight swing  */
+/* between R and 2R), one window of D rows: row r is consumed and its     */
+/* registers are re-armed at once with row r + D, so D rows stay in       */
+/* flight all the time, across page boundaries.  One unrolled trip of D   */
+/* rows, 64/D trips per page: the smallest code of all variants.          */
+/* ------------------------------------------------------------------ */
+template <int D, bool VERIFY, int MINB, int THREADS = kLdgThreads>
+__global__ void __launch_bounds__(THREADS, MINB)
+scan_roll_kernel(ScanArgs a)
+{
+	__shared__ unsigned long long s_tot[STROM_T_COUNT];
+	constexpr int NT = 64 / D;
+	constexpr uint32_t FULL = 0xFFFFFFFFu;
+	constexpr int DV = VERIFY ? D : 1;
+	const uint32_t lane = threadIdx.x & 31, k = lane & 7, gbase = lane & ~7u;
+	const uint32_t n_pages = (uint32_t)a.n_pages;
+	const uint32_t n_groups = (gridDim.x * THREADS) >> 3;
+	uint32_t page = (blockIdx.x * THREADS + threadIdx.x) >> 3;
+	const uint32_t seed0 = kLaneSeed[4 * k], seed1 = kLaneSeed[4 * k + 1],
+				   seed2 = kLaneSeed[4 * k + 2], seed3 = kLaneSeed[4 * k + 3];
+
+	if (threadIdx.x < STROM_T_COUNT)
+		s_tot[threadIdx.x] = (threadIdx.x == STROM_T_FIRST_MISMATCH) ? ~0ull : 0ull;
+	__syncthreads();
+
+	if (page - (lane >> 3) < n_pages)
+	{
+		auto row_ptr = [&](const uint4 *base, uint32_t pg) {
+			return base + (size_t)(pg < n_pages ? pg : n_pages - 1) * 512 + k;
+		};
+		const uint4 *p = row_ptr(a.pages, page);
+		const uint4 *q = VERIFY ? row_ptr(a.ref, page) : nullptr;
+		uint4 win[D], rwin[DV];
+
+#pragma unroll
+		for (int r = 0; r < D; r++)
+		{
+			win[r] = ldg_stream(p + r * 8);
+			if (VERIFY) rwin[r] = ldg_stream(q + r * 8);
+		}
+		for (;;)
+		{
+			const uint32_t npage = page + n_groups;
+			const bool more = npage - (lane >> 3) < n_pages;
+			uint32_t s0 = seed0, s1 = seed1, s2 = seed2, s3 = seed3;
+			uint32_t orv = 0, cnt = 0, first_unit = 0xFFFFu;
+			uint32_t hstate = 0, bounds = 0, lp_end = 0;
+
+#pragma unroll 1
+			for (int t = 0; t < NT; t++)
+			{
+				/* where the rows D ahead of this trip live: same page, or the head of the next one */
+				const bool wrap = (t == NT - 1);
+				const bool refill = !wrap || more;
+				const uint4 *src = wrap ? row_ptr(a.pages, npage) : p + (t + 1) * D * 8;
+				const uint4 *rsrc = VERIFY ? (wrap ? row_ptr(a.ref, npage) : q + (t + 1) * D * 8) : nullptr;
+#pragma unroll
+				for (int r = 0; r < D; r++)
+				{
+					const uint32_t row = (uint32_t)t * D + r;
+					uint4 v = win[r];
+					uint4 u = VERIFY ? rwin[r] : v;
+					if (r == 0 && t == 0)
+					{
+						const uint32_t w2 = __shfl_sync(FULL, v.z, gbase);
+						const uint32_t w3 = __shfl_sync(FULL, v.w, gbase);
+						const uint32_t w4 = __shfl_sync(FULL, v.x, gbase + 1);
+						const PageHeader h = decode_header(w2, w3, w4);
+						hstate = pack_header_state(h);
+						bounds = h.upper | (h.special << 16);
+						lp_end = kHdrWords + h.nlp;
+					}
+					orv |= v.x | v.y | v.z | v.w;
+					if (VERIFY)
+					{
+						if (((v.x ^ u.x) | (v.y ^ u.y) | (v.z ^ u.z) | (v.w ^ u.w)) != 0)
+							first_unit = min(first_unit, row * 8 + k);
+					}
+					if (row * 32 < lp_end)
+						cnt += lp_check_row(v.x, v.y, v.z, v.w, row * 32 + 4 * k, bounds & 0xFFFFu, bounds >> 16,
+											lp_end - kHdrWords);
+					if (r == 0 && t == 0 && k == 0)
+						v.z &= 0xFFFF0000u;
+					s0 = fnv_mix(s0, v.x);
+					s1 = fnv_mix(s1, v.y);
+					s2 = fnv_mix(s2, v.z);
+					s3 = fnv_mix(s3, v.w);
+					if (refill)                                   /* re-arm the registers just consumed */
+					{
+						win[r] = ldg_stream(src + r * 8);
+						if (VERIFY) rwin[r] = ldg_stream(rsrc + r * 8);
+					}
+				}
+			}
+			uint32_t hash = fnv_mix(fnv_mix(s0, 0), 0) ^ fnv_mix(fnv_mix(s1, 0), 0) ^
+							fnv_mix(fnv_mix(s2, 0), 0) ^ fnv_mix(fnv_mix(s3, 0), 0);
+#pragma unroll
+			for (int d = 4; d >= 1; d >>= 1)
+			{
+				hash ^= __shfl_xor_sync(FULL, hash, d);
+				orv |= __shfl_xor_sync(FULL, orv, d);
+				cnt += __shfl_xor_sync(FULL, cnt, d);
+				if (VERIFY) first_unit = min(first_unit, __shfl_xor_sync(FULL, first_unit, d));
+			}
+			if (k == 0 && page < n_pages)
+			{
+				const StromPageResult r = finish_page(hash, a.first_blkno + page, orv == 0, unpack_header_state(hstate), cnt);
+				if (a.results)
+					a.results[page] = r;
+				tally_page(s_tot, r, VERIFY ? first_unit : 0xFFFFu, a.base_offset + (uint64_t)page * STROM_BLCKSZ);
+			}
+			if (!more)
+				break;
+			page = npage;
+			p = row_ptr(a.pages, page);
+			if (VERIFY) q = row_ptr(a.ref, page);
+		}
+	}
+	publish_totals(s_tot, a.totals);
+}
+
+/* ------------------------------------------------------------------ */
+/* kernel 4: kernel 2's mapping (8 lanes per page, 4 FNV chains per lane) */
+/* with the rows staged through shared memory by cp.async instead of      */
+/* through registers.  Every lane owns a private ring of D 16-byte slots  */
+/* and keeps D rows in flight (32 instead of 8), crossing page boundaries; */
+/* a lane only ever reads what it requested itself, so no barrier of any  */
+/* kind is needed: cp.async.wait_group is per thread.  The registers that */
+/* kernel 2 spends on its double buffer are free, and the bytes in flight  */
+/* per SM are bounded by shared memory (192KB) instead of the register file */
+/* -- with FEWER pages in flight, which is what shortens a launch's tail.  */
+/* ------------------------------------------------------------------ */
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void *gptr)
+{
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+template <int THREADS, int D, int MINB = 1, bool VERIFY = false>
+__global__ void __launch_bounds__(THREADS, MINB)
+scan_ring_kernel(ScanArgs a)
+{
+	static_assert(64 % D == 0, "the ring depth must divide the 64 rows of a page");
+	extern __shared__ __align__(128) unsigned char smem[];
+	__shared__ unsigned long long s_tot[STROM_T_COUNT];
+	constexpr uint32_t FULL = 0xFFFFFFFFu;
+	constexpr int NT = 64 / D;
+	const uint32_t lane = threadIdx.x & 31, k = lane & 7, gbase = lane & ~7u;
+	const uint32_t n_pages = (uint32_t)a.n_pages;
+	const uint32_t n_groups = (gridDim.x * THREADS) >> 3;
+	uint32_t page = (blockIdx.x * THREADS + threadIdx.x) >> 3;
+	const uint32_t seed0 = kLaneSeed[4 * k], seed1 = kLaneSeed[4 * k + 1],
+				   seed2 = kLaneSeed[4 * k + 2], seed3 = kLaneSeed[4 * k + 3];
+	/* slot s of this lane: smem + (s * THREADS + threadIdx.x) * 16 -> a warp reads 512 contiguous bytes */
+	const uint32_t ring = smem_u32(smem) + threadIdx.x * 16;
+	constexpr uint32_t kRefRing = (uint32_t)THREADS * D * 16;   /* VERIFY: a second ring for the other copy */
+
+	if (threadIdx.x < STROM_T_COUNT)
+		s_tot[threadIdx.x] = (threadIdx.x == STROM_T_FIRST_MISMATCH) ? ~0ull : 0ull;
+	__syncthreads();
+
+	if (page - (lane >> 3) < n_pages)
+	{
+		auto row_ptr = [&](const uint4 *base, uint32_t pg) {
+			return base + (size_t)(pg < n_pages ? pg : n_pages - 1) * 512 + k;
+		};
+		const uint4 *p = row_ptr(a.pages, page);
+		const uint4 *q = VERIFY ? row_ptr(a.ref, page) : nullptr;
+		/* prologue: the first D rows of the first page */
+#pragma unroll
+		for (int r = 0; r < D; r++)
+		{
+			cp_async16(ring + (uint32_t)r * THREADS * 16, p + r * 8);
+			if (VERIFY) cp_async16(ring + kRefRing + (uint32_t)r * THREADS * 16, q + r * 8);
+			cp_async_commit();
+		}
+		for (;;)
+		{
+			const uint32_t npage = page + n_groups;
+			const bool more = npage - (lane >> 3) < n_pages;
+			uint32_t s0 = seed0, s1 = seed1, s2 = seed2, s3 = seed3;
+			uint32_t orv = 0, cnt = 0, first_unit = 0xFFFFu;
+			uint32_t hstate = 0, bounds = 0, lp_end = 0;
+
+#pragma unroll 1
+			for (int t = 0; t < NT; t++)
+			{
+				const bool wrap = (t == NT - 1);
+				const bool refill = !wrap || more;
+				const uint4 *src = wrap ? row_ptr(a.pages, npage) : p + (t + 1) * D * 8;
+				const uint4 *rsrc = VERIFY ? (wrap ? row_ptr(a.ref, npage) : q + (t + 1) * D * 8) : nullptr;
+#pragma unroll
+				for (int r = 0; r < D; r++)
+				{
+					const uint32_t row = (uint32_t)t * D + r;
+					cp_async_wait<D - 1>();                   /* the oldest outstanding row has landed */
+					uint4 v;
+					asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+								 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+								 : "r"(ring + (uint32_t)r * THREADS * 16) : "memory");
+					uint4 u = v;
+					if (VERIFY)
+						asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+									 : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+									 : "r"(ring + kRefRing + (uint32_t)r * THREADS * 16) : "memory");
+					if (refill)
+					{
+						cp_async16(ring + (uint32_t)r * THREADS * 16, src + r * 8);
+						if (VERIFY) cp_async16(ring + kRefRing + (uint32_t)r * THREADS * 16, rsrc + r * 8);
+					}
+					cp_async_commit();                        /* empty groups keep the count in step */
+					if (VERIFY && ((v.x ^ u.x) | (v.y ^ u.y) | (v.z ^ u.z) | (v.w ^ u.w)) != 0)
+						first_unit = min(first_unit, row * 8 + k);
+					if (r == 0 && t == 0)
+					{
+						const uint32_t w2 = __shfl_sync(FULL, v.z, gbase);
+						const uint32_t w3 = __shfl_sync(FULL, v.w, gbase);
+						const uint32_t w4 = __shfl_sync(FULL, v.x, gbase + 1);
+						const PageHeader h = decode_header(w2, w3, w4);
+						hstate = pack_header_state(h);
+						bounds = h.upper | (h.special << 16);
+						lp_end = kHdrWords + h.nlp;
+					}
+					orv |= v.x | v.y | v.z | v.w;
+					if (row * 32 < lp_end)
+						cnt += lp_check_row(v.x, v.y, v.z, v.w, row * 32 + 4 * k, bounds & 0xFFFFu, bounds >> 16,
+											lp_end - kHdrWords);
+					if (r == 0 && t == 0 && k == 0)
+						v.z &= 0xFFFF0000u;
+					s0 = fnv_mix(s0, v.x);
+					s1 = fnv_mix(s1, v.y);
+					s2 = fnv_mix(s2, v.z);
+					s3 = fnv_mix(s3, v.w);
+				}
+			}
+			uint32_t hash = fnv_mix(fnv_mix(s0, 0), 0) ^ fnv_mix(fnv_mix(s1, 0), 0) ^
+							fnv_mix(fnv_mix(s2, 0), 0) ^ fnv_mix(fnv_mix(s3, 0), 0);
+#pragma unroll
+			for (int d = 4; d >= 1; d >>= 1)
+			{
+				hash ^= __shfl_xor_sync(FULL, hash, d);
+				orv |= __shfl_xor_sync(FULL, orv, d);
+				cnt += __shfl_xor_sync(FULL, cnt, d);
+				if (VERIFY) first_unit = min(first_unit, __shfl_xor_sync(FULL, first_unit, d));
+			}
+			if (k == 0 && page < n_pages)
+			{
+				const StromPageResult r = finish_page(hash, a.first_blkno + page, orv == 0, unpack_header_state(hstate), cnt);
+				if (a.results)
+					a.results[page] = r;
+				tally_page(s_tot, r, VERIFY ? first_unit : 0xFFFFu, a.base_offset + (uint64_t)page * STROM_BLCKSZ);
+			}
+			if (!more)
+				break;
+			page = npage;
+			p = row_ptr(a.pages, page);
+			if (VERIFY) q = row_ptr(a.ref, page);
+		}
+		cp_async_wait<0>();
+	}
+	publish_totals(s_tot, a.totals);
+}
+
+/* ------------------------------------------------------------------ */
 /* kernel 3: one warp per page, lane j = column j, whole page in registers */
 /*                                                                        */
 /* The time a launch loses at its end is about one "page time" (how long  */
@@ -467,17 +951,20 @@ static DeviceInfo *device_info()
 
 /* NVME_STROM_SCAN_VARIANT = "tma:W:S" (warps, slots per warp) | "ldg:R:B" (rows
  * in flight, min blocks per SM); default picked by measurement */
-struct Variant { bool tma; int a, b; bool dyn = false; bool col = false; };
+struct Variant { bool tma; int a, b; bool dyn = false; bool col = false; bool ring = false; bool lean = false; bool roll = false; };
 static Variant pick_variant(uint32_t flags)
 {
-	Variant v = {false, 8, 2};      /* measured on B200: ldg:8:2 reaches 0.97 of the copy peak */
+	Variant v = {false, 0, 0};      /* a == 0: the measured default, chosen by size below */
 	const char *e = getenv("NVME_STROM_SCAN_VARIANT");
 	if (e && !strncmp(e, "tma:", 4)) { v.tma = true; sscanf(e + 4, "%d:%d", &v.a, &v.b); }
+	else if (e && !strncmp(e, "roll:", 5)) { v.tma = false; v.roll = true; v.a = 16; v.b = 2; sscanf(e + 5, "%d:%d", &v.a, &v.b); }
+	else if (e && !strncmp(e, "lean:", 5)) { v.tma = false; v.lean = true; v.a = 8; v.b = 2; sscanf(e + 5, "%d:%d", &v.a, &v.b); }
+	else if (e && !strncmp(e, "ring:", 5)) { v.tma = false; v.ring = true; v.a = 384; v.b = 32; sscanf(e + 5, "%d:%d", &v.a, &v.b); }
 	else if (e && !strncmp(e, "col:", 4)) { v.tma = false; v.col = true; v.a = atoi(e + 4); }
 	else if (e && !strncmp(e, "ldgdyn", 6)) { v.tma = false; v.a = 8; v.b = 2; v.dyn = true; }
 	else if (e && !strncmp(e, "ldg:", 4)) { v.tma = false; v.a = 8; v.b = 2; sscanf(e + 4, "%d:%d", &v.a, &v.b); }
-	if (flags & STROM_SCAN_KERNEL_LDG) { if (v.tma) { v.tma = false; v.a = 8; v.b = 2; } }
-	if (flags & STROM_SCAN_KERNEL_TMA) { if (!v.tma) { v.tma = true; v.a = 8; v.b = 3; } }
+	if (flags & STROM_SCAN_KERNEL_LDG) { v = Variant{false, 8, 2}; }
+	if (flags & STROM_SCAN_KERNEL_TMA) { v = Variant{true, 8, 3}; }
 	return v;
 }
 
@@ -531,6 +1018,88 @@ static int launch_ldg(DeviceInfo *d, int slot, const ScanArgs &a_in, cudaStream_
 	return 0;
 }
 
+template <int D, bool V, int MINB, int THREADS = kLdgThreads>
+static int launch_roll(DeviceInfo *d, const ScanArgs &a, cudaStream_t st)
+{
+	static int occ[64];
+	int dev = (int)(d - g_dev);
+	if (occ[dev] == 0)
+	{
+		int n = 0;
+		STROM_CUDA_OR_FAIL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_roll_kernel<D, V, MINB, THREADS>,
+																		 THREADS, 0));
+		occ[dev] = n > 0 ? n : 1;
+	}
+	if (a.n_pages >= 0xFFE00000ull)
+	{
+		set_error("scan: more than 2^32 - 2^21 pages in one launch");
+		errno = EINVAL;
+		return -1;
+	}
+	uint64_t want = (a.n_pages * 8 + THREADS - 1) / THREADS;
+	uint64_t cap = (uint64_t)d->sm_count * occ[dev];
+	int grid = (int)(want < cap ? want : cap);
+	scan_roll_kernel<D, V, MINB, THREADS><<<grid, THREADS, 0, st>>>(a);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	return 0;
+}
+
+template <int R, bool V, int MINB, int THREADS = kLdgThreads>
+static int launch_lean(DeviceInfo *d, const ScanArgs &a, cudaStream_t st)
+{
+	static int occ[64];
+	int dev = (int)(d - g_dev);
+	if (occ[dev] == 0)
+	{
+		int n = 0;
+		STROM_CUDA_OR_FAIL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_lean_kernel<R, V, MINB, THREADS>,
+																		 THREADS, 0));
+		occ[dev] = n > 0 ? n : 1;
+	}
+	if (a.n_pages >= 0xFFE00000ull)
+	{
+		set_error("scan: more than 2^32 - 2^21 pages in one launch");
+		errno = EINVAL;
+		return -1;
+	}
+	uint64_t want = (a.n_pages * 8 + THREADS - 1) / THREADS;
+	uint64_t cap = (uint64_t)d->sm_count * occ[dev];
+	int grid = (int)(want < cap ? want : cap);
+	scan_lean_kernel<R, V, MINB, THREADS><<<grid, THREADS, 0, st>>>(a);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	return 0;
+}
+
+template <int THREADS, int D, int MINB = 1, bool VERIFY = false>
+static int launch_ring(DeviceInfo *d, int slot, const ScanArgs &a, cudaStream_t st)
+{
+	(void)slot;
+	static bool attr_set[64];
+	const int dev = (int)(d - g_dev);
+	const size_t smem = (size_t)THREADS * D * 16 * (VERIFY ? 2 : 1);
+	if (!attr_set[dev])
+	{
+		STROM_CUDA_OR_FAIL(cudaFuncSetAttribute(scan_ring_kernel<THREADS, D, MINB, VERIFY>,
+												cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		attr_set[dev] = true;
+	}
+	if (a.n_pages >= 0xFFE00000ull)
+	{
+		set_error("scan: more than 2^32 - 2^21 pages in one launch");
+		errno = EINVAL;
+		return -1;
+	}
+	uint64_t want = (a.n_pages * 8 + THREADS - 1) / THREADS;
+	uint64_t cap = (uint64_t)d->sm_count * MINB;
+	int grid = (int)(want < cap ? want : cap);
+	scan_ring_kernel<THREADS, D, MINB, VERIFY><<<grid, THREADS, smem, st>>>(a);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	return 0;
+}
+
 template <int W>
 static int launch_col(DeviceInfo *d, const ScanArgs &a, cudaStream_t st)
 {
@@ -564,7 +1133,15 @@ int preload_kernels()
 	cudaFuncAttributes fa;
 	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, totals_reset_kernel));
 	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, scan_ldg_kernel<8, false, 2, false>));
-	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, scan_ldg_kernel<4, true, 2, false>));
+	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, scan_ring_kernel<512, 16, 1, false>));
+	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, scan_ring_kernel<256, 16, 2, false>));
+	STROM_CUDA_OR_FAIL(cudaFuncGetAttributes(&fa, scan_ring_kernel<256, 16, 1, true>));
+	STROM_CUDA_OR_FAIL(cudaFuncSetAttribute(scan_ring_kernel<512, 16, 1, false>,
+											cudaFuncAttributeMaxDynamicSharedMemorySize, 512 * 16 * 16));
+	STROM_CUDA_OR_FAIL(cudaFuncSetAttribute(scan_ring_kernel<256, 16, 2, false>,
+											cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 16 * 16));
+	STROM_CUDA_OR_FAIL(cudaFuncSetAttribute(scan_ring_kernel<256, 16, 1, true>,
+											cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 16 * 16 * 2));
 	DeviceInfo *d = device_info();
 	if (!d)
 		return -1;
@@ -611,6 +1188,64 @@ extern "C" int strom_scan_pages_dev(const void *d_pages, uint64_t n_pages, uint3
 		if (v.a == 14 && v.b == 2) return launch_tma<14, 2>(d, 6, a, st);
 		return launch_tma<8, 3>(d, 7, a, st);
 	}
+	if (!v.tma && v.a == 0)
+	{
+		/* measured on B200 (profiles/): rings of 16 rows; one 512-thread block per SM for long
+		 * launches, two 256-thread blocks for short ones (they start and drain faster) */
+		if (n_pages >= 32768)
+			return launch_ring<512, 16>(d, 0, a, st);
+		return launch_ring<256, 16, 2>(d, 0, a, st);
+	}
+	if (v.roll)
+	{
+		if (v.a == 8 && v.b == 2)   return launch_roll<8, false, 2>(d, a, st);
+		if (v.a == 8 && v.b == 3)   return launch_roll<8, false, 3>(d, a, st);
+		if (v.a == 8 && v.b == 4)   return launch_roll<8, false, 4>(d, a, st);
+		if (v.a == 16 && v.b == 1)  return launch_roll<16, false, 1>(d, a, st);
+		if (v.a == 16 && v.b == 128) return launch_roll<16, false, 5, 128>(d, a, st);
+		if (v.a == 16 && v.b == 160) return launch_roll<16, false, 3, 160>(d, a, st);
+		if (v.a == 32 && v.b == 1)  return launch_roll<32, false, 1>(d, a, st);
+		if (v.a == 8 && v.b == 320) return launch_roll<8, false, 2, 320>(d, a, st);
+		if (v.a == 8 && v.b == 224) return launch_roll<8, false, 3, 224>(d, a, st);
+		return launch_roll<16, false, 2>(d, a, st);
+	}
+	if (v.lean)
+	{
+		if (v.a == 4 && v.b == 2)  return launch_lean<4, false, 2>(d, a, st);
+		if (v.a == 4 && v.b == 3)  return launch_lean<4, false, 3>(d, a, st);
+		if (v.a == 4 && v.b == 4)  return launch_lean<4, false, 4>(d, a, st);
+		if (v.a == 8 && v.b == 3)  return launch_lean<8, false, 3>(d, a, st);
+		if (v.a == 16 && v.b == 1) return launch_lean<16, false, 1>(d, a, st);
+		if (v.a == 16 && v.b == 2) return launch_lean<16, false, 2>(d, a, st);
+		if (v.a == 8 && v.b == 192) return launch_lean<8, false, 3, 192>(d, a, st);
+		if (v.a == 8 && v.b == 128) return launch_lean<8, false, 5, 128>(d, a, st);
+		if (v.a == 8 && v.b == 160) return launch_lean<8, false, 3, 160>(d, a, st);
+		if (v.a == 8 && v.b == 96)  return launch_lean<8, false, 6, 96>(d, a, st);
+		if (v.a == 8 && v.b == 64)  return launch_lean<8, false, 9, 64>(d, a, st);
+		if (v.a == 4 && v.b == 192) return launch_lean<4, false, 4, 192>(d, a, st);
+		return launch_lean<8, false, 2>(d, a, st);
+	}
+	if (v.ring)
+	{
+		if (v.a == 256 && v.b == 32) return launch_ring<256, 32>(d, 8, a, st);
+		if (v.a == 320 && v.b == 32) return launch_ring<320, 32>(d, 9, a, st);
+		if (v.a == 448 && v.b == 32) return launch_ring<448, 32>(d, 10, a, st);
+		if (v.a == 512 && v.b == 16) return launch_ring<512, 16>(d, 11, a, st);
+		if (v.a == 768 && v.b == 16) return launch_ring<768, 16>(d, 12, a, st);
+		if (v.a == 192 && v.b == 64) return launch_ring<192, 64>(d, 13, a, st);
+		if (v.a == 224 && v.b == 64) return launch_ring<224, 64>(d, 14, a, st);
+		if (v.a == 576 && v.b == 16) return launch_ring<576, 16>(d, 0, a, st);
+		if (v.a == 640 && v.b == 16) return launch_ring<640, 16>(d, 0, a, st);
+		if (v.a == 448 && v.b == 16) return launch_ring<448, 16>(d, 0, a, st);
+		if (v.a == 384 && v.b == 16) return launch_ring<384, 16>(d, 0, a, st);
+		if (v.a == 256 && v.b == 16) return launch_ring<256, 16, 2>(d, 0, a, st);
+		if (v.a == 320 && v.b == 16) return launch_ring<320, 16, 2>(d, 0, a, st);
+		if (v.a == 192 && v.b == 16) return launch_ring<192, 16, 3>(d, 0, a, st);
+		if (v.a == 128 && v.b == 16) return launch_ring<128, 16, 4>(d, 0, a, st);
+		if (v.a == 256 && v.b == 8)  return launch_ring<256, 8, 3>(d, 0, a, st);
+		if (v.a == 512 && v.b == 8)  return launch_ring<512, 8, 2>(d, 0, a, st);
+		return launch_ring<384, 32>(d, 15, a, st);
+	}
 	if (v.col)
 	{
 		if (v.a == 8)  return launch_col<8>(d, a, st);
@@ -643,6 +1278,14 @@ extern "C" int strom_scan_verify_pages_dev(const void *d_pages, const void *d_re
 	ScanArgs a = {(const uint4 *)d_pages, (const uint4 *)d_ref, n_pages, base_offset, first_blkno,
 				  d_results, (unsigned long long *)d_totals};
 	const char *e = getenv("NVME_STROM_FUSED_R");
+	if (!e || atoi(e) == 0)                 /* default: shared-memory rings, 2 x 64KB per SM */
+		return launch_ring<256, 16, 1, true>(d, 0, a, (cudaStream_t)stream);
+	if (atoi(e) == 384)
+		return launch_ring<384, 16, 1, true>(d, 0, a, (cudaStream_t)stream);
+	if (atoi(e) == 192)
+		return launch_ring<192, 16, 2, true>(d, 0, a, (cudaStream_t)stream);
+	if (atoi(e) == 448)
+		return launch_ring<448, 16, 1, true>(d, 0, a, (cudaStream_t)stream);
 	if (e && atoi(e) == 41)
 		return launch_ldg<4, true, 1>(d, 13, a, (cudaStream_t)stream);
 	if (e && atoi(e) == 2)

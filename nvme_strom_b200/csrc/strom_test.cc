@@ -97,11 +97,13 @@ static void wait_for_segment(Slot *s)
 	w.dma_task_id = s->uarg.dma_task_id;
 	TRACE("slot %d: wait gpu task %lu", s->index, w.dma_task_id);
 	int rv = nvme_strom_ioctl(STROM_IOCTL__MEMCPY_WAIT, &w);
+	const int wait_errno = errno;
 	if (w.status)
 	{
 		printf("async dma (id=%lu, status=%ld)\n", w.dma_task_id, w.status);
 		fflush(stdout);
 	}
+	errno = wait_errno;
 	SYS_OK(rv == 0, "STROM_IOCTL__MEMCPY_WAIT");
 	if (enable_checks)
 	{

@@ -9,7 +9,10 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 VARIANTS = ["tma:8:3", "tma:4:6", "tma:6:4", "tma:12:2", "tma:7:4", "tma:16:1", "tma:8:2", "tma:14:2",
-            "ldg:8:2", "ldg:4:2", "ldg:4:3", "ldg:8:1", "ldg:4:1", "ldgdyn", "col:12", "col:10", "col:8", "col:6", "col:4"]
+            "ldg:8:2", "ldg:4:2", "ldg:4:3", "ldg:8:1", "ldg:4:1", "ldgdyn", "col:12", "col:10", "col:8", "col:6", "col:4",
+            "roll:16:2", "roll:8:2", "roll:8:3", "roll:8:320", "roll:8:224", "roll:16:1", "roll:32:1", "roll:16:160",
+            "lean:8:2", "lean:4:2", "lean:4:3", "lean:4:4", "lean:8:3", "lean:16:1",
+            "ring:384:32", "ring:256:32", "ring:320:32", "ring:448:32", "ring:512:16", "ring:768:16", "ring:192:64", "ring:224:64"]
 
 
 @pytest.fixture(params=VARIANTS)

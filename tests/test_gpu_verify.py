@@ -60,10 +60,13 @@ def test_block_map(oracle):
     assert verify_dev(to_dev(a), to_dev(b), n, to_dev(perm)) == want
 
 
-@pytest.mark.parametrize("fused_r", ["4", "2", "41"])
+@pytest.mark.parametrize("fused_r", ["", "384", "192", "448", "4", "2", "41"])
 def test_fused_scan_and_verify(oracle, monkeypatch, fused_r):
     from gpu_util import scan_verify_dev, to_dev
-    monkeypatch.setenv("NVME_STROM_FUSED_R", fused_r)
+    if fused_r:
+        monkeypatch.setenv("NVME_STROM_FUSED_R", fused_r)       # "" = the default (shared-memory rings)
+    else:
+        monkeypatch.delenv("NVME_STROM_FUSED_R", raising=False)
     for n in (1, 3, 4, 37, 1500):
         a = oracle.gen_pages(0x5EED0001, 9, n, mixed=True)
         b = a.copy()

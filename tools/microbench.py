@@ -57,8 +57,8 @@ def main():
     best, med = timed(lambda: ref.copy_(buf), reps)
     print(f"torch copy_ (r+w)         best {2 * nbytes / best / 1e6:8.1f} GB/s  median {2 * nbytes / med / 1e6:8.1f}")
 
-    variants = ["tma:8:3", "tma:4:6", "tma:6:4", "tma:12:2", "tma:7:4", "tma:16:1", "tma:8:2", "tma:14:2",
-                "ldg:8:2", "ldg:4:2", "ldg:4:3", "ldg:8:1", "ldg:4:1"]
+    variants = ["ring:512:16", "ring:256:16", "ring:384:32", "lean:8:2", "ldg:8:2", "ldg:4:3", "roll:16:2",
+                "col:12", "tma:16:1", "tma:8:3"]
     rows = []
     for v in variants:
         os.environ["NVME_STROM_SCAN_VARIANT"] = v
@@ -69,13 +69,13 @@ def main():
     os.environ.pop("NVME_STROM_SCAN_VARIANT")
     best, med = timed(lambda: abi.check(lib.strom_verify_pages_dev(pb, pf, n_pages, None, 0, pt, None), "v"), reps)
     print(f"verify (2 buffers)        best {2 * nbytes / best / 1e6:8.1f} GB/s  median {2 * nbytes / med / 1e6:8.1f}  frac {2 * nbytes / med / 1e6 / peak:.3f}")
-    for r in ("4", "2", "41"):
+    for r in ("0", "384", "192", "448", "4"):
         os.environ["NVME_STROM_FUSED_R"] = r
         best, med = timed(lambda: abi.check(lib.strom_scan_verify_pages_dev(pb, pf, n_pages, 0, 0, 0, pr, pt, None), "f"), reps)
         print(f"fused scan+verify R={r:3s}   best {2 * nbytes / best / 1e6:8.1f} GB/s  median {2 * nbytes / med / 1e6:8.1f}  frac {2 * nbytes / med / 1e6 / peak:.3f}")
     # small launches: one 32MB segment (what the pipeline launches per slot)
     seg_pages = 4096
-    for v in ("tma:8:3", "ldg:8:2"):
+    for v in ("ring:256:16", "ring:512:16", "ldg:8:2"):
         os.environ["NVME_STROM_SCAN_VARIANT"] = v
         best, med = timed(lambda: abi.check(lib.strom_scan_pages_dev(pb, seg_pages, 0, 0, pr, pt, None), "s"), reps)
         print(f"scan {v:10s} 32MB seg   best {best * 1e3:7.1f} us  median {med * 1e3:7.1f} us  ({seg_pages * 8192 / med / 1e6:.0f} GB/s, L2-resident)")
