@@ -55,13 +55,21 @@ static pthread_mutex_t buffer_lock = PTHREAD_MUTEX_INITIALIZER;
 static char *device_buffer;
 static StromScanTotals *d_totals;
 
+/* leave without running destructors: reader threads and the CUDA runtime are still busy */
+static void die(void)
+{
+	fflush(stdout);
+	fflush(stderr);
+	_exit(1);
+}
+
 #define CUDA_OK(call)                                                                       \
 	do {                                                                                    \
 		cudaError_t rc__ = (call);                                                          \
 		if (rc__ != cudaSuccess)                                                            \
 		{                                                                                   \
 			fprintf(stderr, "%d: failed on %s: %s\n", __LINE__, #call, cudaGetErrorName(rc__)); \
-			exit(1);                                                                        \
+			die();                                                                          \
 		}                                                                                   \
 	} while (0)
 #define SYS_OK(cond, what)                                                  \
@@ -69,7 +77,7 @@ static StromScanTotals *d_totals;
 		if (!(cond))                                                        \
 		{                                                                   \
 			fprintf(stderr, "%d: failed on %s: %m\n", __LINE__, what);      \
-			exit(1);                                                        \
+			die();                                                          \
 		}                                                                   \
 	} while (0)
 
