@@ -34,6 +34,8 @@
 #include <sched.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
+#include <sys/vfs.h>
+#include <fcntl.h>
 #include <thread>
 #include <unistd.h>
 
@@ -137,7 +139,47 @@ static int fetch_piece(const Job &j, char *dst)
 SourceMap::~SourceMap()
 {
 	if (base)
+	{
+		if (region_state)
+			for (uint64_t r = 0; r * kRegion < size; r++)
+				if (region_state[r].load() == 1)
+					(void)cudaHostUnregister(base + r * kRegion);
+		(void)cudaGetLastError();
 		munmap(base, size);
+	}
+}
+
+/* true when [off, off+len) is page-locked for CUDA (registering it now if it was not) */
+bool SourceMap::region_ready(uint64_t off, uint64_t len)
+{
+	if (!pinnable || off + len > size)
+		return false;
+	for (uint64_t r = off / kRegion; r * kRegion < off + len; r++)
+	{
+		int st = region_state[r].load(std::memory_order_acquire);
+		if (st == 0)
+		{
+			std::lock_guard<std::mutex> g(region_lock);
+			st = region_state[r].load();
+			if (st == 0)
+			{
+				const uint64_t start = r * kRegion;
+				const uint64_t bytes = std::min<uint64_t>(kRegion, (size - start + 4095) & ~4095ull);
+				cudaError_t rc = cudaHostRegister(base + start, bytes, cudaHostRegisterPortable);
+				(void)cudaGetLastError();
+				st = rc == cudaSuccess ? 1 : 2;
+				if (st == 2)
+				{
+					pinnable = false;                       /* do not try the other regions either */
+					logf(1, "source mapping cannot be page-locked (%s): staged copies", cudaGetErrorName(rc));
+				}
+				region_state[r].store(st, std::memory_order_release);
+			}
+		}
+		if (st != 1)
+			return false;
+	}
+	return true;
 }
 
 std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st)
@@ -153,16 +195,46 @@ std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st)
 		const SourceMap &m = *cache[i];
 		if (m.dev == (uint64_t)st.st_dev && m.ino == (uint64_t)st.st_ino)
 		{
-			if (m.size == (uint64_t)st.st_size && m.mtime_s == st.st_mtim.tv_sec && m.mtime_ns == st.st_mtim.tv_nsec)
+			/* a MAP_SHARED view always shows the file's current bytes; only a size change makes
+			 * the mapping stale.  (mtime is useless here: page-locking a writable shared mapping
+			 * of a tmpfs file touches it.) */
+			if (m.size == (uint64_t)st.st_size)
 				return cache[i];
-			cache.erase(cache.begin() + (long)i);      /* file changed: map it afresh */
+			cache.erase(cache.begin() + (long)i);
 			break;
 		}
 	}
-	void *p = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_SHARED, fd, 0);
+	/* tmpfs / hugetlbfs pages can be pinned: map writable-shared (what cudaHostRegister wants)
+	 * through a read-write reopen; everything else gets a plain read-only view */
+	static const bool want_pin = [] { const char *e = getenv("NVME_STROM_PIN_SOURCE"); return !(e && atoi(e) == 0); }();
+	void *p = MAP_FAILED;
+	bool pinnable = false;
+	struct statfs sfs;
+	if (want_pin && fstatfs(fd, &sfs) == 0 && (sfs.f_type == 0x01021994 /* tmpfs */ || sfs.f_type == 0x958458f6 /* hugetlbfs */))
+	{
+		char path[64];
+		snprintf(path, sizeof(path), "/proc/self/fd/%d", fd);
+		int rw = open(path, O_RDWR | O_CLOEXEC);
+		if (rw >= 0)
+		{
+			p = mmap(nullptr, (size_t)st.st_size, PROT_READ | PROT_WRITE, MAP_SHARED, rw, 0);
+			close(rw);
+			pinnable = (p != MAP_FAILED);
+		}
+	}
+	if (p == MAP_FAILED)
+		p = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_SHARED, fd, 0);
 	if (p == MAP_FAILED)
 		return nullptr;
 	auto m = std::make_shared<SourceMap>();
+	m->pinnable = pinnable;
+	if (pinnable)
+	{
+		const uint64_t n = ((uint64_t)st.st_size + SourceMap::kRegion - 1) / SourceMap::kRegion;
+		m->region_state.reset(new std::atomic<int>[n]);
+		for (uint64_t i = 0; i < n; i++)
+			m->region_state[i].store(0);
+	}
 	m->dev = (uint64_t)st.st_dev;
 	m->ino = (uint64_t)st.st_ino;
 	m->size = (uint64_t)st.st_size;
@@ -240,6 +312,11 @@ private:
 		if (!s.task)
 			return;
 		cudaError_t rc = cudaEventSynchronize(s.ev);
+		if (rc != cudaSuccess)
+		{
+			logf(0, "engine(dev=%d): copy failed: %s", device_, cudaGetErrorName(rc));
+			(void)cudaGetLastError();
+		}
 		stats_dma_finished(s.tsc);
 		task_put(s.task, rc == cudaSuccess ? 0 : -EIO);
 		s.task = nullptr;
@@ -316,6 +393,42 @@ private:
 			next = (next + 1) % n_slots;
 			retire(s);                            /* slot's previous copy must be done */
 			const uint64_t t0 = rdtsc_now();
+			/* page-locked source (tmpfs): the copy engine reads the page cache itself */
+			if (j.src && !j.direct && !g_skip_h2d.load(std::memory_order_relaxed) &&
+				const_cast<SourceMap *>(j.src)->region_ready(j.file_off, j.length))
+			{
+				if (int frc = injected_fault())
+				{
+					task_put(j.task, frc);
+					continue;
+				}
+				stats_dma_started();
+				/* one copy per registered region: a source range must lie inside one registration */
+				cudaError_t cr = cudaSuccess;
+				for (uint64_t done = 0; done < j.length && cr == cudaSuccess;)
+				{
+					const uint64_t off = j.file_off + done;
+					const uint64_t room = SourceMap::kRegion - (off % SourceMap::kRegion);
+					const uint64_t n = std::min<uint64_t>(j.length - done, room);
+					cr = cudaMemcpyAsync(j.dst + done, j.src->base + off, n, cudaMemcpyHostToDevice, stream);
+					done += n;
+				}
+				if (cr == cudaSuccess)
+					cr = cudaEventRecord(s.ev, stream);
+				if (cr != cudaSuccess)
+				{
+					logf(0, "engine(dev=%d): copy from page-locked source failed: %s", device_, cudaGetErrorName(cr));
+					(void)cudaGetLastError();
+					stats_dma_finished(t0);
+					task_put(j.task, -EIO);
+				}
+				else
+				{
+					s.task = j.task;
+					s.tsc = t0;
+				}
+				continue;
+			}
 			int rc = fetch_piece(j, s.buf);
 			if (rc == 0 && g_skip_h2d.load(std::memory_order_relaxed))
 			{

@@ -71,6 +71,15 @@ struct SourceMap {
 	uint64_t dev = 0, ino = 0, size = 0;
 	long mtime_s = 0, mtime_ns = 0;
 	char *base = nullptr;
+	/* Files whose pages can be pinned (tmpfs, hugetlbfs) are page-locked for CUDA region by
+	 * region on first touch; the copy engine then reads the page cache itself and the piece
+	 * needs neither a CPU copy nor a staging slot.  ext4/xfs refuse (file-backed shared
+	 * mappings cannot be pinned for long): those stay on the staged path. */
+	bool pinnable = false;
+	static constexpr uint64_t kRegion = 64ull << 20;
+	std::unique_ptr<std::atomic<int>[]> region_state;      /* 0 untouched, 1 registered, 2 refused */
+	std::mutex region_lock;
+	bool region_ready(uint64_t off, uint64_t len);          /* registers on demand */
 	~SourceMap();
 };
 std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st);   /* null: use pread */
