@@ -193,7 +193,11 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 	in.file = &finfo;
 	in.page_state = split ? state.data() : nullptr;
 	in.n_state_pages = state.size();
-	in.piece_max = engine_piece_for((uint64_t)arg->nr_chunks * arg->chunk_sz);
+	/* the mapped view of the source (null: pread).  A page-locked source (tmpfs) needs no
+	 * staging, so its pieces can be as long as the request is contiguous. */
+	std::shared_ptr<SourceMap> source = want_direct_io() ? nullptr : source_map_get(arg->file_desc, st);
+	in.piece_max = (source && source->pinnable) ? (64u << 20)
+												: engine_piece_for((uint64_t)arg->nr_chunks * arg->chunk_sz);
 	Plan plan;
 	if ((rc = plan_chunks(in, &plan)) != 0)
 		return rc;
@@ -212,7 +216,7 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 	if (want_direct_io())
 		task->fd_direct = open_direct_twin(own_fd);
 	else
-		task->source = source_map_get(own_fd, st);
+		task->source = source;
 	const unsigned long task_id = task->id;
 
 	/* chunks that are mostly in the page cache come back through wb_buffer,

@@ -429,37 +429,61 @@ private:
 				}
 				continue;
 			}
-			int rc = fetch_piece(j, s.buf);
-			if (rc == 0 && g_skip_h2d.load(std::memory_order_relaxed))
+			/* staged path.  A piece planned for a page-locked source can be longer than a slot
+			 * (calibration mode, a refused registration, a range past EOF): feed it through the
+			 * slots in slot-sized parts, each holding its own reference on the task. */
+			Slot *cur = &s;
+			for (uint32_t done = 0; done < j.length;)
 			{
-				task_put(j.task, 0);              /* source-rate calibration: read, do not copy */
-				continue;
-			}
-			if (rc == 0)
-			{
-				stats_dma_started();
-				cudaError_t cr = cudaMemcpyAsync(j.dst, s.buf, j.length, cudaMemcpyHostToDevice, stream);
-				if (cr == cudaSuccess)
-					cr = cudaEventRecord(s.ev, stream);
-				if (cr != cudaSuccess)
+				const uint32_t n = std::min<uint32_t>(slot_sz, j.length - done);
+				const bool last_part = done + n == j.length;
+				if (!last_part)
+					task_add_ref(j.task, 1);
+				if (done > 0)
 				{
-					(void)cudaGetLastError();
-					stats_dma_finished(t0);
-					rc = -EIO;
+					cur = &slots[(size_t)next];
+					next = (next + 1) % n_slots;
+					retire(*cur);
 				}
-			}
-			if (stat_info_level() > 0)
-			{
-				const uint64_t t1 = rdtsc_now();
-				g_stats.nr_submit_dma++;
-				g_stats.clk_submit_dma += t1 > t0 ? t1 - t0 : 0;
-			}
-			if (rc != 0)
-				task_put(j.task, rc);
-			else
-			{
-				s.task = j.task;
-				s.tsc = t0;
+				Job part = j;
+				part.file_off = j.file_off + done;
+				part.length = n;
+				part.dst = j.dst + done;
+				const uint64_t tp = rdtsc_now();
+				int rc = fetch_piece(part, cur->buf);
+				if (rc == 0 && g_skip_h2d.load(std::memory_order_relaxed))
+				{
+					task_put(j.task, 0);              /* source-rate calibration: read, do not copy */
+					done += n;
+					continue;
+				}
+				if (rc == 0)
+				{
+					stats_dma_started();
+					cudaError_t cr = cudaMemcpyAsync(part.dst, cur->buf, n, cudaMemcpyHostToDevice, stream);
+					if (cr == cudaSuccess)
+						cr = cudaEventRecord(cur->ev, stream);
+					if (cr != cudaSuccess)
+					{
+						(void)cudaGetLastError();
+						stats_dma_finished(tp);
+						rc = -EIO;
+					}
+				}
+				if (stat_info_level() > 0)
+				{
+					const uint64_t t1 = rdtsc_now();
+					g_stats.nr_submit_dma++;
+					g_stats.clk_submit_dma += t1 > tp ? t1 - tp : 0;
+				}
+				if (rc != 0)
+					task_put(j.task, rc);
+				else
+				{
+					cur->task = j.task;
+					cur->tsc = tp;
+				}
+				done += n;
 			}
 		}
 		for (Slot &s : slots)
