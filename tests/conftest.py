@@ -12,6 +12,11 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    # a fresh checkout has no built artefacts (they are git-ignored): build them once
+    lib = os.path.join(ROOT, "nvme_strom_b200", "lib", "libnvme_strom.so")
+    tool = os.path.join(ROOT, "nvme_strom_b200", "bin", "strom_test")
+    if not (os.path.exists(lib) and os.path.exists(tool)):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "nvme_strom_b200", "csrc"), "-j8"])
 
 
 class Oracle:
