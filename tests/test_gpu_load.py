@@ -258,3 +258,34 @@ print("split", a.nr_ram2gpu, a.nr_ssd2gpu)
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "split" in r.stdout
+
+
+@pytest.mark.parametrize("env", [{"NVME_STROM_IO": "direct"}, {"NVME_STROM_SRC": "pread"}, {"NVME_STROM_FIEMAP": "0"},
+                                 {"NVME_STROM_READERS": "1", "NVME_STROM_SLOT_KB": "128", "NVME_STROM_SLOTS": "2"},
+                                 {"NVME_STROM_WC": "1", "NVME_STROM_PIECE_DIV": "3"}])
+def test_io_modes_land_the_same_bytes(heapfile, env):
+    """O_DIRECT, pread, no FIEMAP, a single reader with tiny slots: same bytes, same counters.
+    The switches are read once per process, so each mode runs in a child."""
+    code = r'''
+import os, sys
+import numpy as np, torch
+sys.path.insert(0, %r); sys.path.insert(0, os.path.join(%r, "tests"))
+from gpu_util import map_gpu, ssd2gpu, wait
+path = %r
+data = np.fromfile(path, dtype=np.uint8)
+fd = os.open(path, os.O_RDONLY)
+rng = np.random.default_rng(9)
+ids = list(range(4096, 8192)) + rng.integers(0, 16384, 200).tolist()
+buf = torch.zeros(len(ids) * 8192, dtype=torch.uint8, device="cuda")
+m = map_gpu(buf)
+a, keep = ssd2gpu(m.handle, 0, fd, ids)
+assert wait(a.dma_task_id) == 0
+got = buf.cpu().numpy().reshape(-1, 8192)
+want = data.reshape(-1, 8192)[np.array(list(keep))]
+assert (got == want).all()
+assert a.nr_ssd2gpu == len(ids) and a.nr_dma_blocks == len(ids) * 16
+print("ok", a.nr_dma_submit)
+''' % (ROOT, ROOT, heapfile)
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr

@@ -135,3 +135,38 @@ def test_cached_chunks_go_to_the_tail(oracle, strom):
     assert rc == 0 and cnt[:2] == [2, 5]
     assert out == [0, 1, 3, 5, 7, 6, 2]
     assert (rc, cnt, out) == run_oracle(oracle, *args)[:3]
+
+
+def test_fiemap_view_of_a_real_file(strom, tmp_path):
+    """the extent map the planner uses in place of ext4_get_block / xfs_get_blocks
+    (kmod/nvme_strom.c:153-165): sorted, non-overlapping, covers the file; on file systems
+    without FIEMAP (tmpfs) the planner falls back to an identity map (0 extents)"""
+    import os
+    p = tmp_path / "ext.heap"
+    assert strom.lib.strom_heapgen_file(str(p).encode(), 3, 0, 4096, 0, 2) == 0      # 32 MiB
+    fd = os.open(str(p), os.O_RDONLY)
+    os.fsync(fd)
+    buf = np.zeros(3 * 4096, dtype=np.uint64)
+    fn = strom.lib.strom_file_extents_debug
+    fn.argtypes = [C.c_int, C.c_void_p, C.c_uint32]
+    n = fn(fd, buf.ctypes.data, 4096)
+    os.close(fd)
+    assert n >= 0
+    if n == 0:
+        pytest.skip("file system has no FIEMAP (identity map is used)")
+    ext = buf[:3 * n].reshape(-1, 3)
+    assert (ext[:, 2] > 0).all() and (ext[:, 0] % 4096 == 0).all()
+    assert (ext[1:, 0] >= ext[:-1, 0] + ext[:-1, 2]).all()           # sorted, no overlap
+    assert ext[0, 0] == 0 and ext[-1, 0] + ext[-1, 2] >= 32 << 20    # covers the file
+
+
+def test_requests_break_at_extent_boundaries(oracle, strom):
+    """physically discontiguous extents end a <=128KB request early (:1370-1381)"""
+    ids = list(range(64))                                            # 512 KB, 8KB chunks
+    contiguous = [(0, 128, 1000)]
+    broken = [(0, 10, 1000), (10, 50, 90000), (60, 68, 5000)]        # 4KB pages: breaks at 40KB and 240KB
+    a = run_product(strom, True, ids, 8192, 0, 1 << 20, None, contiguous, 0, 1 << 20, 0)
+    b = run_product(strom, True, ids, 8192, 0, 1 << 20, None, broken, 0, 1 << 20, 0)
+    assert a[1] == [0, 64, 4, 1024] and b[1][2] == 6 and b[1][3] == 1024
+    assert b[:3] == run_oracle(oracle, True, ids, 8192, 0, 1 << 20, None, broken, 0, 1 << 20, 0)[:3]
+    assert len(a[3]) == len(b[3]) == 1                               # one transfer piece either way: pread does not care
