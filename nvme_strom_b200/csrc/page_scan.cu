@@ -25,9 +25,12 @@
  */
 #include "common.h"
 #include "page_math.cuh"
+#include "strom_internal.h"
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <utility>
+#include <vector>
 
 namespace strom {
 
@@ -1076,14 +1079,28 @@ template <int THREADS, int D, int MINB = 1, bool VERIFY = false>
 static int launch_ring(DeviceInfo *d, int slot, const ScanArgs &a, cudaStream_t st)
 {
 	(void)slot;
-	static bool attr_set[64];
-	const int dev = (int)(d - g_dev);
 	const size_t smem = (size_t)THREADS * D * 16 * (VERIFY ? 2 : 1);
-	if (!attr_set[dev])
+	/* the opt-in to > 48KB of dynamic shared memory belongs to the function as loaded in the
+	 * CURRENT context; a process may use several contexts per device (nvme_test creates its
+	 * own), so remember it per (device, context) rather than per device */
 	{
-		STROM_CUDA_OR_FAIL(cudaFuncSetAttribute(scan_ring_kernel<THREADS, D, MINB, VERIFY>,
-												cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		attr_set[dev] = true;
+		static std::mutex lock;
+		static std::vector<std::pair<int, void *>> done;
+		void *ctx = nullptr;
+		const DriverApi &api = driver_api();
+		if (api.ok)
+			(void)api.cuCtxGetCurrent(&ctx);
+		const std::pair<int, void *> key((int)(d - g_dev), ctx);
+		std::lock_guard<std::mutex> g(lock);
+		bool seen = false;
+		for (const auto &k : done)
+			seen = seen || k == key;
+		if (!seen)
+		{
+			STROM_CUDA_OR_FAIL(cudaFuncSetAttribute(scan_ring_kernel<THREADS, D, MINB, VERIFY>,
+													cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+			done.push_back(key);
+		}
 	}
 	if (a.n_pages >= 0xFFE00000ull)
 	{
