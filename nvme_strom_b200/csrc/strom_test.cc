@@ -9,8 +9,12 @@
  * tool fetches the comparison copy into a host DMA buffer with
  * MEMCPY_SSD2RAM, sends it up, and runs the fused checksum + validation +
  * byte-compare kernel on the two device copies.  -k runs the page scan alone.
+ * -d takes a list ("-d 0,1,2,3"): the segments of the file are then split into
+ * contiguous ranges, one per GPU (strom_partition_segments), every GPU runs its
+ * own slots, streams and transfer engine, and the counters are merged on the
+ * host at the end -- no device-to-device traffic at all.
  *
- * Structure: the main thread submits segments (MEMCPY_SSD2GPU, and
+ * Structure per GPU: a submit thread issues segments (MEMCPY_SSD2GPU, and
  * MEMCPY_SSD2RAM for -c) as slots free up; a completion thread takes them in
  * submission order, sits in MEMCPY_WAIT, then queues the upload of the
  * comparison copy and the kernels on the slot's stream; a stream callback
@@ -41,7 +45,6 @@
 
 #define BLCKSZ 8192
 
-static int device_index = 0;
 static int nr_segments = 6;
 static size_t segment_sz = 32UL << 20;
 static int enable_checks = 0;
@@ -49,11 +52,8 @@ static int enable_scan = 0;
 static int print_mapping = 0;
 static int test_by_vfs = 0;
 static size_t vfs_io_size = 0;
-
-static sem_t buffer_sem;
-static pthread_mutex_t buffer_lock = PTHREAD_MUTEX_INITIALIZER;
-static char *device_buffer;
-static StromScanTotals *d_totals;
+static int debug_trace = 0;
+#define TRACE(...) do { if (debug_trace) { fprintf(stderr, __VA_ARGS__); fputc('\n', stderr); } } while (0)
 
 /* leave without running destructors: reader threads and the CUDA runtime are still busy */
 static void die(void)
@@ -81,7 +81,10 @@ static void die(void)
 		}                                                                   \
 	} while (0)
 
+struct GpuRun;
+
 struct Slot {
+	GpuRun *run;
 	int index;
 	int is_running;
 	size_t fpos;
@@ -94,8 +97,28 @@ struct Slot {
 	int file_desc;
 };
 
-static int debug_trace = 0;
-#define TRACE(...) do { if (debug_trace) { fprintf(stderr, __VA_ARGS__); fputc('\n', stderr); } } while (0)
+/* everything one GPU needs for its share of the file */
+struct GpuRun {
+	int device = 0;
+	int fdesc = -1;
+	size_t first_byte = 0, n_bytes = 0;          /* its contiguous range of the file */
+	char *device_buffer = nullptr;
+	StromScanTotals *d_totals = nullptr;
+	unsigned long handle = 0;
+	std::vector<Slot> slots;
+	sem_t buffer_sem;
+	pthread_mutex_t buffer_lock = PTHREAD_MUTEX_INITIALIZER;
+	/* submission-ordered hand-over from the submit thread to the completion thread */
+	std::vector<Slot *> fifo;
+	size_t fifo_head = 0;
+	bool fifo_closed = false;
+	pthread_mutex_t fifo_lock = PTHREAD_MUTEX_INITIALIZER;
+	pthread_cond_t fifo_cond = PTHREAD_COND_INITIALIZER;
+	/* results */
+	long usec_sem_wait = 0, nr_ram2gpu = 0, nr_ssd2gpu = 0, nr_dma_submit = 0, nr_dma_blocks = 0;
+	StromScanTotals totals;
+	double seconds = 0;
+};
 
 static void wait_for_segment(Slot *s)
 {
@@ -103,7 +126,7 @@ static void wait_for_segment(Slot *s)
 
 	memset(&w, 0, sizeof(w));
 	w.dma_task_id = s->uarg.dma_task_id;
-	TRACE("slot %d: wait gpu task %lu", s->index, w.dma_task_id);
+	TRACE("gpu %d slot %d: wait gpu task %lu", s->run->device, s->index, w.dma_task_id);
 	int rv = nvme_strom_ioctl(STROM_IOCTL__MEMCPY_WAIT, &w);
 	const int wait_errno = errno;
 	if (w.status)
@@ -117,7 +140,6 @@ static void wait_for_segment(Slot *s)
 	{
 		w.dma_task_id = s->rarg.dma_task_id;
 		rv = nvme_strom_ioctl(STROM_IOCTL__MEMCPY_WAIT, &w);
-		TRACE("slot %d: ram task %lu done rv=%d", s->index, w.dma_task_id, rv);
 		SYS_OK(rv == 0, "STROM_IOCTL__MEMCPY_WAIT (comparison copy)");
 	}
 }
@@ -125,25 +147,25 @@ static void wait_for_segment(Slot *s)
 static void CUDART_CB cb_release(void *priv)
 {
 	Slot *s = static_cast<Slot *>(priv);
+	GpuRun *g = s->run;
 
-	TRACE("slot %d: release", s->index);
-	pthread_mutex_lock(&buffer_lock);
+	pthread_mutex_lock(&g->buffer_lock);
 	s->is_running = 0;
-	pthread_mutex_unlock(&buffer_lock);
-	sem_post(&buffer_sem);
+	pthread_mutex_unlock(&g->buffer_lock);
+	sem_post(&g->buffer_sem);
 }
 
-static Slot *take_slot(std::vector<Slot> &slots, size_t fpos, long *usec_wait)
+static Slot *take_slot(GpuRun *g, size_t fpos)
 {
 	struct timeval t1, t2;
 
 	gettimeofday(&t1, NULL);
-	SYS_OK(sem_wait(&buffer_sem) == 0, "sem_wait");
+	SYS_OK(sem_wait(&g->buffer_sem) == 0, "sem_wait");
 	gettimeofday(&t2, NULL);
-	*usec_wait += (t2.tv_sec - t1.tv_sec) * 1000000L + (t2.tv_usec - t1.tv_usec);
-	pthread_mutex_lock(&buffer_lock);
+	g->usec_sem_wait += (t2.tv_sec - t1.tv_sec) * 1000000L + (t2.tv_usec - t1.tv_usec);
+	pthread_mutex_lock(&g->buffer_lock);
 	Slot *found = NULL;
-	for (Slot &s : slots)
+	for (Slot &s : g->slots)
 		if (!s.is_running)
 		{
 			s.is_running = 1;
@@ -151,20 +173,13 @@ static Slot *take_slot(std::vector<Slot> &slots, size_t fpos, long *usec_wait)
 			found = &s;
 			break;
 		}
-	pthread_mutex_unlock(&buffer_lock);
+	pthread_mutex_unlock(&g->buffer_lock);
 	if (!found)
 	{
 		fprintf(stderr, "Bug? no free slot but semaphore > 0\n");
-		exit(1);
+		die();
 	}
 	return found;
-}
-
-static void drain(std::vector<Slot> &slots, long *usec_wait)
-{
-	for (Slot &s : slots)
-		CUDA_OK(cudaStreamSynchronize(s.stream));
-	(void)usec_wait;
 }
 
 static void print_size(const char *label, double v, const char *suffix)
@@ -179,12 +194,12 @@ static void print_size(const char *label, double v, const char *suffix)
 		printf("%s%.2fGB%s", label, v / (double)(1UL << 30), suffix);
 }
 
-static void show_throughput(size_t file_size, struct timeval tv1, struct timeval tv2, long usec_sem_wait,
-							long nr_ram2gpu, long nr_ssd2gpu, long nr_dma_submit, long nr_dma_blocks)
+/* same lines as utils/nvme_test.c:325-380 */
+static void show_throughput(size_t file_size, double seconds, long usec_sem_wait, long nr_ram2gpu, long nr_ssd2gpu,
+							long nr_dma_submit, long nr_dma_blocks)
 {
-	double usec = (tv2.tv_sec - tv1.tv_sec) * 1e6 + (tv2.tv_usec - tv1.tv_usec);
-	long time_ms = (long)(usec / 1000.0);
-	double throughput = (double)file_size / (usec / 1e6);
+	long time_ms = (long)(seconds * 1000.0);
+	double throughput = (double)file_size / seconds;
 
 	print_size("read: ", (double)file_size, "");
 	if (time_ms < 4000)
@@ -205,76 +220,47 @@ static void show_throughput(size_t file_size, struct timeval tv1, struct timeval
 	putchar('\n');
 }
 
-static void report_checks(int fdesc)
-{
-	StromScanTotals t;
-
-	CUDA_OK(cudaMemcpy(&t, d_totals, sizeof(t), cudaMemcpyDeviceToHost));
-	if (enable_scan || enable_checks)
-		printf("scan: pages=%lu zero=%lu checksum_fail=%lu header_fail=%lu lp_bad_pages=%lu invalid=%lu "
-			   "n_normal=%lu n_bad_lp=%lu xor=%lu sum=%lu\n",
-			   t.v[STROM_T_PAGES], t.v[STROM_T_ZERO], t.v[STROM_T_CHECKSUM_FAIL], t.v[STROM_T_HEADER_FAIL],
-			   t.v[STROM_T_LP_BAD_PAGES], t.v[STROM_T_INVALID], t.v[STROM_T_N_NORMAL], t.v[STROM_T_N_BAD_LP],
-			   t.v[STROM_T_XOR_CHECKSUM], t.v[STROM_T_SUM_CHECKSUM]);
-	if (!enable_checks)
-		return;
-	printf("verify: mismatch_blocks=%lu\n", t.v[STROM_T_MISMATCH_BLOCKS]);
-	if (t.v[STROM_T_MISMATCH_BLOCKS] == 0)
-		return;
-	/* the reference dumps the neighbourhood of the first difference and exits 1 (:133-194).
-	 * The slot that held the block has been reused by now, so load that one block again and
-	 * dump it against the file's bytes in the same format. */
-	uint64_t off = t.v[STROM_T_FIRST_MISMATCH] & ~(uint64_t)(BLCKSZ - 1);
-	std::vector<char> src(BLCKSZ), dst(BLCKSZ);
-	fprintf(stderr, "first difference at file offset 0x%lx\n", t.v[STROM_T_FIRST_MISMATCH]);
-	if (pread(fdesc, src.data(), BLCKSZ, (off_t)off) == BLCKSZ)
-	{
-		uint32_t id = (uint32_t)(off / BLCKSZ);
-		StromCmd__MemCopySsdToGpu u;
-		StromCmd__MapGpuMemory m;
-		memset(&m, 0, sizeof(m));
-		m.vaddress = (uint64_t)device_buffer;
-		m.length = BLCKSZ;
-		if (nvme_strom_ioctl(STROM_IOCTL__MAP_GPU_MEMORY, &m) == 0)
-		{
-			memset(&u, 0, sizeof(u));
-			u.handle = m.handle;
-			u.file_desc = fdesc;
-			u.nr_chunks = 1;
-			u.chunk_sz = BLCKSZ;
-			u.chunk_ids = &id;
-			StromCmd__MemCopyWait w = {0, 0};
-			if (nvme_strom_ioctl(STROM_IOCTL__MEMCPY_SSD2GPU, &u) == 0)
-			{
-				w.dma_task_id = u.dma_task_id;
-				nvme_strom_ioctl(STROM_IOCTL__MEMCPY_WAIT, &w);
-				CUDA_OK(cudaMemcpy(dst.data(), device_buffer, BLCKSZ, cudaMemcpyDeviceToHost));
-				strom_memdump_on_corruption(src.data(), dst.data(), BLCKSZ, stdout);
-			}
-		}
-	}
-	fprintf(stderr, "memory corruption detected\n");
-	exit(1);
-}
-
-static void setup_slots(std::vector<Slot> &slots, int fdesc, unsigned long handle)
+static void setup_gpu(GpuRun *g)
 {
 	const unsigned nr_chunks = (unsigned)(segment_sz / BLCKSZ);
+	const size_t buffer_size = segment_sz * (size_t)nr_segments;
 
-	SYS_OK(sem_init(&buffer_sem, 0, (unsigned)nr_segments) == 0, "sem_init");
-	slots.resize((size_t)nr_segments);
+	CUDA_OK(cudaSetDevice(g->device));
+	CUDA_OK(cudaMalloc((void **)&g->device_buffer, buffer_size));
+	CUDA_OK(cudaMemset(g->device_buffer, 0x41, buffer_size));
+	CUDA_OK(cudaMalloc((void **)&g->d_totals, sizeof(StromScanTotals)));
+	if (strom_totals_reset_dev(g->d_totals, NULL) != 0)
+	{
+		fprintf(stderr, "strom_totals_reset_dev: %s\n", strom_last_error());
+		die();
+	}
+	CUDA_OK(cudaDeviceSynchronize());
+	StromCmd__MapGpuMemory map;
+	memset(&map, 0, sizeof(map));
+	map.vaddress = (uint64_t)g->device_buffer;
+	map.length = buffer_size;
+	if (nvme_strom_ioctl(STROM_IOCTL__MAP_GPU_MEMORY, &map) != 0)
+	{
+		fprintf(stderr, "STROM_IOCTL__MAP_GPU_MEMORY(%p, %zu) --> %m\n", (void *)g->device_buffer, buffer_size);
+		die();
+	}
+	g->handle = map.handle;
+
+	SYS_OK(sem_init(&g->buffer_sem, 0, (unsigned)nr_segments) == 0, "sem_init");
+	g->slots.resize((size_t)nr_segments);
 	for (int i = 0; i < nr_segments; i++)
 	{
-		Slot &s = slots[(size_t)i];
+		Slot &s = g->slots[(size_t)i];
+		s.run = g;
 		s.index = i;
 		s.is_running = 0;
 		s.fpos = 0;
-		s.file_desc = dup(fdesc);
+		s.file_desc = dup(g->fdesc);
 		SYS_OK(s.file_desc >= 0, "dup");
 		s.chunk_ids.resize(nr_chunks);
 		s.ram_ids.resize(nr_chunks);
 		memset(&s.uarg, 0, sizeof(s.uarg));
-		s.uarg.handle = handle;
+		s.uarg.handle = g->handle;
 		s.uarg.offset = (size_t)i * segment_sz;
 		s.uarg.file_desc = s.file_desc;
 		s.uarg.nr_chunks = nr_chunks;
@@ -286,7 +272,7 @@ static void setup_slots(std::vector<Slot> &slots, int fdesc, unsigned long handl
 		s.ref_dev = NULL;
 		CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
 		if (test_by_vfs)
-			CUDA_OK(cudaHostAlloc((void **)&s.host_buf, segment_sz, cudaHostAllocDefault));
+			CUDA_OK(cudaHostAlloc((void **)&s.host_buf, segment_sz, cudaHostAllocPortable));
 		if (enable_checks && !test_by_vfs)
 		{
 			/* comparison copy: ALLOC_DMA_BUFFER + mmap, as utils/ssd2ram_test.c:126-147 */
@@ -298,7 +284,7 @@ static void setup_slots(std::vector<Slot> &slots, int fdesc, unsigned long handl
 			s.host_buf = (char *)mmap(NULL, segment_sz, PROT_READ | PROT_WRITE, MAP_SHARED, a.dmabuf_fdesc, 0);
 			SYS_OK(s.host_buf != MAP_FAILED, "mmap(DMA buffer)");
 			close(a.dmabuf_fdesc);
-			CUDA_OK(cudaHostRegister(s.host_buf, segment_sz, cudaHostRegisterDefault));
+			CUDA_OK(cudaHostRegister(s.host_buf, segment_sz, cudaHostRegisterPortable));
 			memset(&s.rarg, 0, sizeof(s.rarg));
 			s.rarg.dest_uaddr = s.host_buf;
 			s.rarg.file_desc = s.file_desc;
@@ -313,64 +299,59 @@ static void setup_slots(std::vector<Slot> &slots, int fdesc, unsigned long handl
 
 static void launch_checks(Slot *s)
 {
+	GpuRun *g = s->run;
 	const uint64_t n_pages = segment_sz / BLCKSZ;
 	const uint32_t first_blkno = (uint32_t)(s->fpos / BLCKSZ);
-	char *landed = device_buffer + s->uarg.offset;
+	char *landed = g->device_buffer + s->uarg.offset;
 
 	if (enable_checks)
 	{
 		CUDA_OK(cudaMemcpyAsync(s->ref_dev, s->host_buf, segment_sz, cudaMemcpyHostToDevice, s->stream));
-		if (strom_scan_verify_pages_dev(landed, s->ref_dev, n_pages, first_blkno, 0, s->fpos, NULL, d_totals,
+		if (strom_scan_verify_pages_dev(landed, s->ref_dev, n_pages, first_blkno, 0, s->fpos, NULL, g->d_totals,
 										s->stream) != 0)
 		{
 			fprintf(stderr, "strom_scan_verify_pages_dev: %s\n", strom_last_error());
-			exit(1);
+			die();
 		}
 	}
 	else if (enable_scan)
 	{
-		if (strom_scan_pages_dev(landed, n_pages, first_blkno, 0, NULL, d_totals, s->stream) != 0)
+		if (strom_scan_pages_dev(landed, n_pages, first_blkno, 0, NULL, g->d_totals, s->stream) != 0)
 		{
 			fprintf(stderr, "strom_scan_pages_dev: %s\n", strom_last_error());
-			exit(1);
+			die();
 		}
 	}
 }
 
-/* submission-ordered hand-over from the main thread to the completion thread */
-static std::vector<Slot *> ready_fifo;
-static size_t fifo_head = 0;
-static bool fifo_closed = false;
-static pthread_mutex_t fifo_lock = PTHREAD_MUTEX_INITIALIZER;
-static pthread_cond_t fifo_cond = PTHREAD_COND_INITIALIZER;
-static void launch_checks(Slot *s);
-
-static void fifo_push(Slot *s)
+static void fifo_push(GpuRun *g, Slot *s)
 {
-	pthread_mutex_lock(&fifo_lock);
+	pthread_mutex_lock(&g->fifo_lock);
 	if (s)
-		ready_fifo.push_back(s);
+		g->fifo.push_back(s);
 	else
-		fifo_closed = true;
-	pthread_cond_signal(&fifo_cond);
-	pthread_mutex_unlock(&fifo_lock);
+		g->fifo_closed = true;
+	pthread_cond_signal(&g->fifo_cond);
+	pthread_mutex_unlock(&g->fifo_lock);
 }
 
-static void *completion_thread(void *)
+static void *completion_thread(void *arg)
 {
-	CUDA_OK(cudaSetDevice(device_index));
+	GpuRun *g = static_cast<GpuRun *>(arg);
+
+	CUDA_OK(cudaSetDevice(g->device));
 	for (;;)
 	{
-		pthread_mutex_lock(&fifo_lock);
-		while (fifo_head == ready_fifo.size() && !fifo_closed)
-			pthread_cond_wait(&fifo_cond, &fifo_lock);
-		if (fifo_head == ready_fifo.size())
+		pthread_mutex_lock(&g->fifo_lock);
+		while (g->fifo_head == g->fifo.size() && !g->fifo_closed)
+			pthread_cond_wait(&g->fifo_cond, &g->fifo_lock);
+		if (g->fifo_head == g->fifo.size())
 		{
-			pthread_mutex_unlock(&fifo_lock);
+			pthread_mutex_unlock(&g->fifo_lock);
 			break;
 		}
-		Slot *s = ready_fifo[fifo_head++];
-		pthread_mutex_unlock(&fifo_lock);
+		Slot *s = g->fifo[g->fifo_head++];
+		pthread_mutex_unlock(&g->fifo_lock);
 		wait_for_segment(s);
 		launch_checks(s);
 		CUDA_OK(cudaLaunchHostFunc(s->stream, cb_release, s));
@@ -378,58 +359,68 @@ static void *completion_thread(void *)
 	return NULL;
 }
 
-static void exec_test_by_strom(unsigned long handle, int fdesc, size_t file_size)
+static double now_seconds(void)
 {
-	std::vector<Slot> slots;
-	struct timeval tv1, tv2;
-	long usec_sem_wait = 0, nr_ram2gpu = 0, nr_ssd2gpu = 0, nr_dma_submit = 0, nr_dma_blocks = 0;
+	struct timeval tv;
 
+	gettimeofday(&tv, NULL);
+	return (double)tv.tv_sec + 1e-6 * (double)tv.tv_usec;
+}
+
+static void finish_gpu(GpuRun *g, double t0)
+{
+	for (Slot &s : g->slots)
+		CUDA_OK(cudaStreamSynchronize(s.stream));
+	CUDA_OK(cudaMemcpy(&g->totals, g->d_totals, sizeof(g->totals), cudaMemcpyDeviceToHost));
+	g->seconds = now_seconds() - t0;
+}
+
+/* one GPU's share through MEMCPY_SSD2GPU (utils/nvme_test.c:382-498) */
+static void *run_by_strom(void *arg)
+{
+	GpuRun *g = static_cast<GpuRun *>(arg);
 	pthread_t completer;
 
-	setup_slots(slots, fdesc, handle);
-	SYS_OK(pthread_create(&completer, NULL, completion_thread, NULL) == 0, "pthread_create");
-	gettimeofday(&tv1, NULL);
-	for (size_t fpos = 0; fpos < file_size; fpos += segment_sz)
+	CUDA_OK(cudaSetDevice(g->device));
+	SYS_OK(pthread_create(&completer, NULL, completion_thread, g) == 0, "pthread_create");
+	const double t0 = now_seconds();
+	for (size_t fpos = g->first_byte; fpos < g->first_byte + g->n_bytes; fpos += segment_sz)
 	{
-		Slot *s = take_slot(slots, fpos, &usec_sem_wait);
+		Slot *s = take_slot(g, fpos);
 
 		for (unsigned i = 0; i < s->uarg.nr_chunks; i++)
 			s->chunk_ids[i] = s->ram_ids[i] = (uint32_t)(fpos / BLCKSZ + i);
 		SYS_OK(nvme_strom_ioctl(STROM_IOCTL__MEMCPY_SSD2GPU, &s->uarg) == 0, "STROM_IOCTL__MEMCPY_SSD2GPU");
-		nr_ram2gpu += s->uarg.nr_ram2gpu;
-		nr_ssd2gpu += s->uarg.nr_ssd2gpu;
-		nr_dma_submit += s->uarg.nr_dma_submit;
-		nr_dma_blocks += s->uarg.nr_dma_blocks;
+		g->nr_ram2gpu += s->uarg.nr_ram2gpu;
+		g->nr_ssd2gpu += s->uarg.nr_ssd2gpu;
+		g->nr_dma_submit += s->uarg.nr_dma_submit;
+		g->nr_dma_blocks += s->uarg.nr_dma_blocks;
 		if (enable_checks)
 			SYS_OK(nvme_strom_ioctl(STROM_IOCTL__MEMCPY_SSD2RAM, &s->rarg) == 0, "STROM_IOCTL__MEMCPY_SSD2RAM");
-		TRACE("slot %d: submitted fpos=%zu", s->index, fpos);
-		fifo_push(s);
+		TRACE("gpu %d slot %d: submitted fpos=%zu", g->device, s->index, fpos);
+		fifo_push(g, s);
 	}
-	fifo_push(NULL);
+	fifo_push(g, NULL);
 	pthread_join(completer, NULL);
-	drain(slots, &usec_sem_wait);
-	gettimeofday(&tv2, NULL);
-	show_throughput(file_size, tv1, tv2, usec_sem_wait, nr_ram2gpu, nr_ssd2gpu, nr_dma_submit, nr_dma_blocks);
-	report_checks(fdesc);
+	finish_gpu(g, t0);
+	return NULL;
 }
 
 /* utils/nvme_test.c:500-600: pread on the submitting thread into pinned memory, H2D */
-static void exec_test_by_vfs(int fdesc, size_t file_size)
+static void *run_by_vfs(void *arg)
 {
-	std::vector<Slot> slots;
-	struct timeval tv1, tv2;
-	long usec_sem_wait = 0;
+	GpuRun *g = static_cast<GpuRun *>(arg);
 
-	setup_slots(slots, fdesc, 0);
-	gettimeofday(&tv1, NULL);
-	for (size_t offset = 0; offset < file_size; offset += segment_sz)
+	CUDA_OK(cudaSetDevice(g->device));
+	const double t0 = now_seconds();
+	for (size_t offset = g->first_byte; offset < g->first_byte + g->n_bytes; offset += segment_sz)
 	{
-		Slot *s = take_slot(slots, offset, &usec_sem_wait);
+		Slot *s = take_slot(g, offset);
 		size_t count = 0;
 
 		for (size_t pos = 0; pos < segment_sz; pos += vfs_io_size)
 		{
-			ssize_t rv = pread(fdesc, s->host_buf + pos, vfs_io_size, (off_t)(offset + pos));
+			ssize_t rv = pread(g->fdesc, s->host_buf + pos, vfs_io_size, (off_t)(offset + pos));
 			SYS_OK(rv >= 0, "pread");
 			count += (size_t)rv;
 			if ((size_t)rv < vfs_io_size)
@@ -437,15 +428,62 @@ static void exec_test_by_vfs(int fdesc, size_t file_size)
 		}
 		if (count < segment_sz)
 			break;
-		CUDA_OK(cudaMemcpyAsync(device_buffer + s->uarg.offset, s->host_buf, segment_sz, cudaMemcpyHostToDevice,
+		CUDA_OK(cudaMemcpyAsync(g->device_buffer + s->uarg.offset, s->host_buf, segment_sz, cudaMemcpyHostToDevice,
 								s->stream));
 		launch_checks(s);        /* -c compares the landed copy with a second upload of the same staging */
 		CUDA_OK(cudaLaunchHostFunc(s->stream, cb_release, s));
 	}
-	drain(slots, &usec_sem_wait);
-	gettimeofday(&tv2, NULL);
-	show_throughput(file_size, tv1, tv2, usec_sem_wait, 0, 0, 0, 0);
-	report_checks(fdesc);
+	finish_gpu(g, t0);
+	return NULL;
+}
+
+static void report_checks(const std::vector<GpuRun *> &runs)
+{
+	StromScanTotals t;
+
+	memset(&t, 0, sizeof(t));
+	t.v[STROM_T_FIRST_MISMATCH] = ~0ull;
+	for (const GpuRun *g : runs)
+		strom_totals_merge(&t, &g->totals);
+	if (enable_scan || enable_checks)
+		printf("scan: pages=%lu zero=%lu checksum_fail=%lu header_fail=%lu lp_bad_pages=%lu invalid=%lu "
+			   "n_normal=%lu n_bad_lp=%lu xor=%lu sum=%lu\n",
+			   t.v[STROM_T_PAGES], t.v[STROM_T_ZERO], t.v[STROM_T_CHECKSUM_FAIL], t.v[STROM_T_HEADER_FAIL],
+			   t.v[STROM_T_LP_BAD_PAGES], t.v[STROM_T_INVALID], t.v[STROM_T_N_NORMAL], t.v[STROM_T_N_BAD_LP],
+			   t.v[STROM_T_XOR_CHECKSUM], t.v[STROM_T_SUM_CHECKSUM]);
+	if (!enable_checks)
+		return;
+	printf("verify: mismatch_blocks=%lu\n", t.v[STROM_T_MISMATCH_BLOCKS]);
+	if (t.v[STROM_T_MISMATCH_BLOCKS] == 0)
+		return;
+	/* the reference dumps the neighbourhood of the first difference and exits 1 (:133-194).
+	 * The slot that held the block has been reused by now, so load that one block again and
+	 * dump it against the file's bytes in the same format. */
+	GpuRun *g = runs[0];
+	uint64_t off = t.v[STROM_T_FIRST_MISMATCH] & ~(uint64_t)(BLCKSZ - 1);
+	std::vector<char> src(BLCKSZ), dst(BLCKSZ);
+	fprintf(stderr, "first difference at file offset 0x%lx\n", t.v[STROM_T_FIRST_MISMATCH]);
+	CUDA_OK(cudaSetDevice(g->device));
+	if (pread(g->fdesc, src.data(), BLCKSZ, (off_t)off) == BLCKSZ)
+	{
+		uint32_t id = (uint32_t)(off / BLCKSZ);
+		StromCmd__MemCopySsdToGpu u;
+		memset(&u, 0, sizeof(u));
+		u.handle = g->handle;
+		u.file_desc = g->fdesc;
+		u.nr_chunks = 1;
+		u.chunk_sz = BLCKSZ;
+		u.chunk_ids = &id;
+		if (nvme_strom_ioctl(STROM_IOCTL__MEMCPY_SSD2GPU, &u) == 0)
+		{
+			StromCmd__MemCopyWait w = {u.dma_task_id, 0};
+			nvme_strom_ioctl(STROM_IOCTL__MEMCPY_WAIT, &w);
+			CUDA_OK(cudaMemcpy(dst.data(), g->device_buffer, BLCKSZ, cudaMemcpyDeviceToHost));
+			strom_memdump_on_corruption(src.data(), dst.data(), BLCKSZ, stdout);
+		}
+	}
+	fprintf(stderr, "memory corruption detected\n");
+	die();
 }
 
 /* utils/nvme_test.c:605-684 */
@@ -495,7 +533,7 @@ static void usage(const char *cmdname)
 {
 	fprintf(stderr,
 			"usage: %s [OPTIONS] <filename>\n"
-			"    -d <device index>:        (default 0)\n"
+			"    -d <device index>[,<index>...]: (default 0); several = shard the file over them\n"
 			"    -n <num of segments>:     (default 6)\n"
 			"    -s <segment size in MB>:  (default 32MB)\n"
 			"    -c : Enables corruption check on the GPU (default off)\n"
@@ -511,6 +549,7 @@ int main(int argc, char *argv[])
 {
 	int c, fdesc;
 	struct stat stbuf;
+	std::vector<int> devices;
 
 	debug_trace = getenv("STROM_TEST_TRACE") != NULL;
 	setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);     /* slot streams + engine streams: avoid queue sharing */
@@ -518,7 +557,10 @@ int main(int argc, char *argv[])
 	{
 		switch (c)
 		{
-			case 'd': device_index = atoi(optarg); break;
+			case 'd':
+				for (char *tok = strtok(optarg, ","); tok; tok = strtok(NULL, ","))
+					devices.push_back(atoi(tok));
+				break;
 			case 'n': nr_segments = atoi(optarg); break;
 			case 's': segment_sz = (size_t)atoi(optarg) << 20; break;
 			case 'c': enable_checks = 1; break;
@@ -532,9 +574,11 @@ int main(int argc, char *argv[])
 			default: usage(argv[0]); break;
 		}
 	}
+	if (devices.empty())
+		devices.push_back(0);
 	if (nr_segments < 1 || segment_sz == 0 || segment_sz % BLCKSZ)
 		usage(argv[0]);
-	CUDA_OK(cudaSetDevice(device_index));
+	CUDA_OK(cudaSetDevice(devices[0]));
 	if (print_mapping && optind == argc)
 		return print_gpu_memory();
 	if (optind + 1 != argc)
@@ -549,8 +593,8 @@ int main(int argc, char *argv[])
 	fdesc = open(argv[optind], O_RDONLY);
 	SYS_OK(fdesc >= 0, "open");
 	SYS_OK(fstat(fdesc, &stbuf) == 0, "fstat");
-	size_t filesize = ((size_t)stbuf.st_size / segment_sz) * segment_sz;      /* tail dropped, :785 */
-	if (filesize == 0)
+	const uint64_t n_segs = (uint64_t)stbuf.st_size / segment_sz;               /* tail dropped, :785 */
+	if (n_segs == 0)
 	{
 		fprintf(stderr, "file size (%zu) is smaller than segment size (%zu)\n", (size_t)stbuf.st_size, segment_sz);
 		return 1;
@@ -563,30 +607,50 @@ int main(int argc, char *argv[])
 		fprintf(stderr, "STROM_IOCTL__CHECK_FILE('%s') --> %m\n", argv[optind]);
 		return 1;
 	}
-	size_t buffer_size = segment_sz * (size_t)nr_segments;
-	CUDA_OK(cudaMalloc((void **)&device_buffer, buffer_size));
-	CUDA_OK(cudaMemset(device_buffer, 0x41, buffer_size));
-	CUDA_OK(cudaMalloc((void **)&d_totals, sizeof(StromScanTotals)));
-	if (strom_totals_reset_dev(d_totals, NULL) != 0)
+
+	/* one contiguous range of segments per GPU */
+	std::vector<GpuRun *> runs;
+	for (size_t k = 0; k < devices.size(); k++)
 	{
-		fprintf(stderr, "strom_totals_reset_dev: %s\n", strom_last_error());
-		return 1;
-	}
-	CUDA_OK(cudaDeviceSynchronize());
-	StromCmd__MapGpuMemory map;
-	memset(&map, 0, sizeof(map));
-	map.vaddress = (uint64_t)device_buffer;
-	map.length = buffer_size;
-	if (nvme_strom_ioctl(STROM_IOCTL__MAP_GPU_MEMORY, &map) != 0)
-	{
-		fprintf(stderr, "STROM_IOCTL__MAP_GPU_MEMORY(%p, %zu) --> %m\n", (void *)device_buffer, buffer_size);
-		return 1;
+		uint64_t first = 0, count = 0;
+		SYS_OK(strom_partition_segments(n_segs, (uint32_t)devices.size(), (uint32_t)k, &first, &count) == 0,
+			   "strom_partition_segments");
+		GpuRun *g = new GpuRun();
+		g->device = devices[k];
+		g->fdesc = fdesc;
+		g->first_byte = first * segment_sz;
+		g->n_bytes = count * segment_sz;
+		setup_gpu(g);
+		runs.push_back(g);
 	}
 	if (print_mapping)
 		print_gpu_memory();
-	if (test_by_vfs)
-		exec_test_by_vfs(fdesc, filesize);
-	else
-		exec_test_by_strom(map.handle, fdesc, filesize);
+
+	std::vector<pthread_t> threads(runs.size());
+	const double t0 = now_seconds();
+	for (size_t k = 0; k < runs.size(); k++)
+		SYS_OK(pthread_create(&threads[k], NULL, test_by_vfs ? run_by_vfs : run_by_strom, runs[k]) == 0,
+			   "pthread_create");
+	for (size_t k = 0; k < runs.size(); k++)
+		pthread_join(threads[k], NULL);
+	const double wall = now_seconds() - t0;
+
+	long usec_sem_wait = 0, nr_ram2gpu = 0, nr_ssd2gpu = 0, nr_dma_submit = 0, nr_dma_blocks = 0;
+	for (const GpuRun *g : runs)
+	{
+		usec_sem_wait += g->usec_sem_wait;
+		nr_ram2gpu += g->nr_ram2gpu;
+		nr_ssd2gpu += g->nr_ssd2gpu;
+		nr_dma_submit += g->nr_dma_submit;
+		nr_dma_blocks += g->nr_dma_blocks;
+		if (runs.size() > 1)
+		{
+			printf("GPU%d: ", g->device);
+			print_size("", (double)g->n_bytes, "");
+			print_size(" at ", (double)g->n_bytes / g->seconds, "/s\n");
+		}
+	}
+	show_throughput(n_segs * segment_sz, wall, usec_sem_wait, nr_ram2gpu, nr_ssd2gpu, nr_dma_submit, nr_dma_blocks);
+	report_checks(runs);
 	return 0;
 }

@@ -61,3 +61,18 @@ def test_read_error_is_reported(c5_file):
                        env=dict(os.environ, NVME_STROM_FAULT_EVERY="50"))
     assert r.returncode == 1, r.stdout + r.stderr
     assert "MEMCPY_WAIT" in r.stderr and "Input/output error" in r.stderr, r.stdout + r.stderr
+
+
+def test_sharded_over_several_gpus(c5_file):
+    """-d 0,1: contiguous segment ranges per GPU, counters merged on the host -- the same
+    integers as one GPU computes"""
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs two GPUs")
+    devs = ",".join(str(i) for i in range(min(n, 4)))
+    for opts in (["-k"], ["-c"]):
+        r = subprocess.run([TOOL, "-d", devs] + opts + [c5_file], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert parse_scan(r.stdout) == golden()
+        assert r.stdout.count("GPU") >= 2 and "nr_ssd2gpu: 131072" in r.stdout
