@@ -319,8 +319,13 @@ def run_product(args):
             heapgen_file(spath, SEED, pages_mine, first_page=first_page)
             barrier()
             try:
-                for _ in range(2):
-                    pipe.run(spath, first_seg, n_seg)        # first pass page-locks the regions
+                sfd = os.open(spath, os.O_RDONLY)
+                t0 = time.perf_counter()
+                abi.check(lib.nvme_strom_pin_file_range(sfd, first_page * 8192, shard_bytes), "nvme_strom_pin_file_range")   # once, as at relation open
+                pin_s = time.perf_counter() - t0
+                os.close(sfd)
+                for _ in range(3):
+                    pipe.run(spath, first_seg, n_seg)
                 barrier()
                 t0 = time.perf_counter()
                 for _ in range(args.steps):
@@ -333,8 +338,9 @@ def run_product(args):
                 tmpfs = {"value": round(world * GIB / (ms_shm * 1e-3) / 1e9, 2), "unit": "GB/s",
                          "ms_per_step": round(ms_shm, 3), "file_dir": shm,
                          "frac_of_h2d": round(world * GIB / (ms_shm * 1e-3) / 1e9 / h2d_total, 4),
-                         "how": "same steps, file on tmpfs: mapping page-locked by the library, H2D straight "
-                                "from the page cache, no staging copy"}
+                         "pin_seconds_once": round(max_over_ranks(pin_s), 3),
+                         "how": "same steps, file on tmpfs, after nvme_strom_pin_file() page-locked its mapping "
+                                "(once, outside the steps): H2D straight from the page cache, no staging copy"}
             finally:
                 barrier()
                 if rank == 0:

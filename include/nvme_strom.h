@@ -218,6 +218,22 @@ int nvme_strom_close(int token);
 /* same as nvme_strom_ioctl() but attributes new tasks to a session token */
 int nvme_strom_ioctl_on(int token, int cmd, void *arg);
 
+/*
+ * Prepare a source file for zero-copy loading: page-lock its (shared) mapping for CUDA so
+ * that MEMCPY_SSD2GPU copies straight out of the page cache, with no CPU copy and no staging
+ * buffer.  Only files whose pages can be pinned qualify (tmpfs, hugetlbfs); ext4/xfs files
+ * return -1/ENOTSUP and keep using the staged path.  Costs about 150 ms per GiB, once; call it
+ * where a relation that will be scanned repeatedly is opened, with the target device current,
+ * never in the middle of a load.  The source-side counterpart of what MAP_GPU_MEMORY does
+ * for the destination in the reference (nvidia_p2p_get_pages at map time,
+ * kmod/pmemmap.c:250-256); the reference itself never pins source pages -- it reads them
+ * from the SSD.
+ */
+int nvme_strom_pin_file(int fdesc);
+/* the same for [offset, offset + length) only (rounded out to 64MB regions): what one
+ * GPU's share of a file sharded over several processes needs */
+int nvme_strom_pin_file_range(int fdesc, uint64_t offset, uint64_t length);
+
 /* The text the proc entry returns on read(2) (kmod/nvme_strom.c:2036-2061).
  * Copies at most len bytes, returns the number copied. */
 size_t nvme_strom_version(char *buf, size_t len);

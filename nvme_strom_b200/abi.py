@@ -119,6 +119,8 @@ lib.nvme_strom_ioctl_on.argtypes = [C.c_int, C.c_int, C.c_void_p]
 lib.nvme_strom_ioctl_on.restype = C.c_int
 lib.nvme_strom_open.restype = C.c_int
 lib.nvme_strom_close.argtypes = [C.c_int]
+lib.nvme_strom_pin_file.argtypes = [C.c_int]
+lib.nvme_strom_pin_file_range.argtypes = [C.c_int, C.c_uint64, C.c_uint64]
 lib.nvme_strom_version.argtypes = [C.c_char_p, C.c_size_t]
 lib.nvme_strom_version.restype = C.c_size_t
 lib.strom_totals_reset_dev.argtypes = [C.c_void_p, C.c_void_p]

@@ -193,11 +193,15 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 	in.file = &finfo;
 	in.page_state = split ? state.data() : nullptr;
 	in.n_state_pages = state.size();
-	/* the mapped view of the source (null: pread).  A page-locked source (tmpfs) needs no
-	 * staging, so its pieces can be as long as the request is contiguous. */
+	/* the mapped view of the source (null: pread).  Where the source is already page-locked
+	 * (tmpfs, after the background locking has caught up) no staging is needed, so the pieces
+	 * can be as long as the request is contiguous. */
 	std::shared_ptr<SourceMap> source = want_direct_io() ? nullptr : source_map_get(arg->file_desc, st);
-	in.piece_max = (source && source->pinnable) ? (64u << 20)
-												: engine_piece_for((uint64_t)arg->nr_chunks * arg->chunk_sz);
+	const uint64_t req_bytes = (uint64_t)arg->nr_chunks * arg->chunk_sz;
+	const uint64_t first_fpos = arg->nr_chunks ? (uint64_t)(arg->relseg_sz ? arg->chunk_ids[0] % arg->relseg_sz
+																			 : arg->chunk_ids[0]) * arg->chunk_sz : 0;
+	in.piece_max = (source && source->range_locked(first_fpos, req_bytes)) ? (64u << 20)
+																			: engine_piece_for(req_bytes);
 	Plan plan;
 	if ((rc = plan_chunks(in, &plan)) != 0)
 		return rc;

@@ -149,44 +149,135 @@ SourceMap::~SourceMap()
 	}
 }
 
-/* true when [off, off+len) is page-locked for CUDA (registering it now if it was not) */
-bool SourceMap::region_ready(uint64_t off, uint64_t len)
+/*
+ * Page-locking costs about 7 GB/s (cudaHostRegister pins and maps every page), far less than
+ * the staged path moves, so it must never sit in front of a transfer.  A region that is not
+ * locked yet is handed to a background thread and the piece at hand takes the staged path;
+ * once the thread is done, later pieces from that region go zero-copy.  A file read once
+ * never waits for the locking; a file scanned again and again (a relation in shared memory)
+ * soon runs at link speed with no CPU copy.
+ *
+ * Measured on B200: even from a background thread cudaHostRegister holds up the engine's own
+ * cudaMemcpyAsync calls while it runs, so locking during a load costs the load its speed
+ * (5.5 instead of 47 GB/s on a 4 GiB one-shot read).  Hence the default is to lock nothing on
+ * the library's own initiative: an application that will scan a file repeatedly says so once
+ * with nvme_strom_pin_file().  NVME_STROM_PIN_SOURCE: 0 only on request (default),
+ * 1 background, 2 on first touch.
+ */
+static int pin_mode()
+{
+	static const int v = env_int("NVME_STROM_PIN_SOURCE", 0, 0, 2);
+	return v;
+}
+
+struct PinRequest { std::shared_ptr<SourceMap> map; uint64_t region; int device; };
+/* Heap-allocated and never freed, like the engines: the locking thread sleeps on the condition
+ * variable for the life of the process, and destroying a condition variable that has a waiter
+ * (which a static object's destructor would do at exit) blocks forever. */
+struct PinState {
+	std::mutex lock;
+	std::condition_variable cv;
+	std::deque<PinRequest> queue;
+	bool thread_started = false;
+};
+static PinState &pin_state()
+{
+	static PinState *p = new PinState();
+	return *p;
+}
+
+static void pin_region_now(SourceMap &m, uint64_t r)
+{
+	const uint64_t start = r * SourceMap::kRegion;
+	const uint64_t bytes = std::min<uint64_t>(SourceMap::kRegion, (m.size - start + 4095) & ~4095ull);
+	cudaError_t rc = cudaHostRegister(m.base + start, bytes, cudaHostRegisterPortable);
+	(void)cudaGetLastError();
+	if (rc != cudaSuccess)
+	{
+		m.pinnable = false;                               /* do not try the other regions either */
+		logf(1, "source mapping cannot be page-locked (%s): staged copies", cudaGetErrorName(rc));
+	}
+	m.region_state[r].store(rc == cudaSuccess ? 1 : 2, std::memory_order_release);
+}
+
+static void pin_thread_main()
+{
+	for (;;)
+	{
+		PinRequest req;
+		{
+			PinState &ps = pin_state();
+			std::unique_lock<std::mutex> g(ps.lock);
+			ps.cv.wait(g, [&] { return !ps.queue.empty(); });
+			req = ps.queue.front();
+			ps.queue.pop_front();
+		}
+		if (cudaSetDevice(req.device) != cudaSuccess)
+		{
+			(void)cudaGetLastError();
+			req.map->region_state[req.region].store(2);
+			continue;
+		}
+		pin_region_now(*req.map, req.region);
+	}
+}
+
+bool SourceMap::range_locked(uint64_t off, uint64_t len) const
+{
+	if (!pinnable || !region_state || len == 0 || off + len > size)
+		return false;
+	for (uint64_t r = off / kRegion; r * kRegion < off + len; r++)
+		if (region_state[r].load(std::memory_order_acquire) != 1)
+			return false;
+	return true;
+}
+
+/* true when [off, off+len) is page-locked for CUDA; starts the locking when it is not */
+bool SourceMap::region_ready(uint64_t off, uint64_t len, const std::shared_ptr<SourceMap> &self, int device)
 {
 	if (!pinnable || off + len > size)
 		return false;
+	if (pin_mode() == 0)
+		return range_locked(off, len);                        /* only what was locked on request */
+	bool all = true;
 	for (uint64_t r = off / kRegion; r * kRegion < off + len; r++)
 	{
 		int st = region_state[r].load(std::memory_order_acquire);
 		if (st == 0)
 		{
-			std::lock_guard<std::mutex> g(region_lock);
-			st = region_state[r].load();
-			if (st == 0)
+			int expect = 0;
+			if (region_state[r].compare_exchange_strong(expect, 3))       /* 3: being locked */
 			{
-				const uint64_t start = r * kRegion;
-				const uint64_t bytes = std::min<uint64_t>(kRegion, (size - start + 4095) & ~4095ull);
-				cudaError_t rc = cudaHostRegister(base + start, bytes, cudaHostRegisterPortable);
-				(void)cudaGetLastError();
-				st = rc == cudaSuccess ? 1 : 2;
-				if (st == 2)
+				if (pin_mode() == 2)
+					pin_region_now(*this, r);
+				else
 				{
-					pinnable = false;                       /* do not try the other regions either */
-					logf(1, "source mapping cannot be page-locked (%s): staged copies", cudaGetErrorName(rc));
+					PinState &ps = pin_state();
+					std::lock_guard<std::mutex> g(ps.lock);
+					ps.queue.push_back({self, r, device});
+					if (!ps.thread_started)
+					{
+						ps.thread_started = true;
+						std::thread(pin_thread_main).detach();
+					}
+					ps.cv.notify_one();
 				}
-				region_state[r].store(st, std::memory_order_release);
 			}
+			st = region_state[r].load(std::memory_order_acquire);
 		}
 		if (st != 1)
-			return false;
+			all = false;
 	}
-	return true;
+	return all;
 }
 
 std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st)
 {
 	static const bool enabled = [] { const char *e = getenv("NVME_STROM_SRC"); return !(e && !strcmp(e, "pread")); }();
-	static std::mutex lock;
-	static std::vector<std::shared_ptr<SourceMap>> cache;
+	/* leaked on purpose: unmapping and unregistering at exit, after the CUDA runtime has gone,
+	 * buys nothing and can only go wrong */
+	static std::mutex &lock = *new std::mutex();
+	static std::vector<std::shared_ptr<SourceMap>> &cache = *new std::vector<std::shared_ptr<SourceMap>>();
 	if (!enabled || st.st_size <= 0)
 		return nullptr;
 	std::lock_guard<std::mutex> g(lock);
@@ -206,7 +297,7 @@ std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st)
 	}
 	/* tmpfs / hugetlbfs pages can be pinned: map writable-shared (what cudaHostRegister wants)
 	 * through a read-write reopen; everything else gets a plain read-only view */
-	static const bool want_pin = [] { const char *e = getenv("NVME_STROM_PIN_SOURCE"); return !(e && atoi(e) == 0); }();
+	static const bool want_pin = true;                  /* mapping writable-shared costs nothing by itself */
 	void *p = MAP_FAILED;
 	bool pinnable = false;
 	struct statfs sfs;
@@ -395,7 +486,7 @@ private:
 			const uint64_t t0 = rdtsc_now();
 			/* page-locked source (tmpfs): the copy engine reads the page cache itself */
 			if (j.src && !j.direct && !g_skip_h2d.load(std::memory_order_relaxed) &&
-				const_cast<SourceMap *>(j.src)->region_ready(j.file_off, j.length))
+				j.task->source->region_ready(j.file_off, j.length, j.task->source, device_))
 			{
 				if (int frc = injected_fault())
 				{
@@ -532,3 +623,35 @@ void engine_submit(Engine *e, const std::vector<Job> &jobs) { e->submit(jobs); }
 
 #include "strom_debug.h"
 extern "C" int strom_debug_skip_h2d(int on) { return strom::g_skip_h2d.exchange(on ? 1 : 0); }
+
+extern "C" int nvme_strom_pin_file_range(int fdesc, uint64_t offset, uint64_t length)
+{
+	struct stat st;
+	if (fstat(fdesc, &st) != 0)
+		return -1;
+	std::shared_ptr<strom::SourceMap> m = strom::source_map_get(fdesc, st);
+	if (!m || !m->pinnable)
+	{
+		errno = ENOTSUP;                         /* ext4, xfs, ...: pages of a shared file mapping cannot be pinned */
+		return -1;
+	}
+	if (offset >= m->size)
+		return 0;
+	const uint64_t end = std::min<uint64_t>(m->size, length > m->size - offset ? m->size : offset + length);
+	for (uint64_t r = offset / strom::SourceMap::kRegion; r * strom::SourceMap::kRegion < end; r++)
+	{
+		int expect = 0;
+		if (m->region_state[r].compare_exchange_strong(expect, 3))
+			strom::pin_region_now(*m, r);
+		while (m->region_state[r].load() == 3)   /* somebody else is at it */
+			sched_yield();
+		if (m->region_state[r].load() != 1)
+		{
+			errno = EIO;
+			return -1;
+		}
+	}
+	return 0;
+}
+
+extern "C" int nvme_strom_pin_file(int fdesc) { return nvme_strom_pin_file_range(fdesc, 0, ~0ull); }

@@ -72,14 +72,14 @@ struct SourceMap {
 	long mtime_s = 0, mtime_ns = 0;
 	char *base = nullptr;
 	/* Files whose pages can be pinned (tmpfs, hugetlbfs) are page-locked for CUDA region by
-	 * region on first touch; the copy engine then reads the page cache itself and the piece
-	 * needs neither a CPU copy nor a staging slot.  ext4/xfs refuse (file-backed shared
+	 * region, in the background; once a region is locked the copy engine reads the page cache
+	 * itself and a piece needs neither a CPU copy nor a staging slot.  ext4/xfs refuse (file-backed shared
 	 * mappings cannot be pinned for long): those stay on the staged path. */
 	bool pinnable = false;
 	static constexpr uint64_t kRegion = 64ull << 20;
-	std::unique_ptr<std::atomic<int>[]> region_state;      /* 0 untouched, 1 registered, 2 refused */
-	std::mutex region_lock;
-	bool region_ready(uint64_t off, uint64_t len);          /* registers on demand */
+	std::unique_ptr<std::atomic<int>[]> region_state;      /* 0 untouched, 1 locked, 2 refused, 3 in progress */
+	bool region_ready(uint64_t off, uint64_t len, const std::shared_ptr<SourceMap> &self, int device);
+	bool range_locked(uint64_t off, uint64_t len) const;    /* no side effects */
 	~SourceMap();
 };
 std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st);   /* null: use pread */

@@ -1,5 +1,5 @@
-"""Files on tmpfs: the library page-locks the file mapping region by region and lets the copy
-engine read the page cache itself (no staging copy).  Same bytes, same counters."""
+"""Files on tmpfs: after nvme_strom_pin_file() the library copies straight out of the page
+cache (page-locked mapping, no staging copy).  Same bytes, same counters, before and after."""
 import os
 
 import numpy as np
@@ -18,8 +18,33 @@ def shm_file(oracle):
     os.unlink(path)
 
 
-def test_loaded_bytes_and_counters(shm_file, oracle):
+def test_pin_file_is_refused_where_pages_cannot_be_pinned(tmp_path):
+    import errno, ctypes as C
+    from nvme_strom_b200 import abi
+    from nvme_strom_b200.loader import heapgen_file
+    p = str(tmp_path / "ext4.heap")
+    heapgen_file(p, 1, 1024)
+    fd = os.open(p, os.O_RDONLY)
+    rc = abi.lib.nvme_strom_pin_file(fd)
+    e = C.get_errno()
+    os.close(fd)
+    import subprocess
+    fstype = subprocess.run(["stat", "-f", "-c", "%T", p], capture_output=True, text=True).stdout.strip()
+    if fstype == "tmpfs":
+        assert rc == 0
+    else:
+        assert rc == -1 and e == errno.ENOTSUP, (fstype, rc, e)
+
+
+@pytest.mark.parametrize("pin", [False, True])
+def test_loaded_bytes_and_counters(shm_file, oracle, pin):
     import torch
+    from nvme_strom_b200 import abi
+    if pin:
+        pfd = os.open(shm_file, os.O_RDONLY)
+        assert abi.lib.nvme_strom_pin_file(pfd) == 0
+        assert abi.lib.nvme_strom_pin_file(pfd) == 0           # idempotent
+        os.close(pfd)
     from gpu_util import map_gpu, ssd2gpu, unmap_gpu, wait
     from nvme_strom_b200.loader import SegmentPipeline
     data = np.fromfile(shm_file, dtype=np.uint8)

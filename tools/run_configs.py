@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--c4-gib", type=int, default=16)
     ap.add_argument("--dir", default=os.environ.get("NVME_STROM_BENCH_DIR", "/tmp"))
     ap.add_argument("--skip", default="")
+    ap.add_argument("--pin", action="store_true", help="page-lock each rank's share of the file first (tmpfs only)")
     args = ap.parse_args()
     rank, local, world = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     torch.cuda.set_device(local)
@@ -52,6 +53,11 @@ def main():
         pages = gib_per_rank * GIB // 8192
         heapgen_file(path, 0x5EED0001, pages, mixed=mixed, first_page=rank * pages)
         barrier()
+        if args.pin:
+            fd = os.open(path, os.O_RDONLY)
+            abi.check(abi.lib.nvme_strom_pin_file_range(fd, rank * pages * 8192, pages * 8192), "nvme_strom_pin_file_range")
+            os.close(fd)
+            barrier()
         return path
 
     def timed_run(pipe, path, first_seg, n_seg, reps=2):
@@ -98,7 +104,7 @@ def main():
             out.append({"config": "C3 sharded load+scan", "n_gpus": world, "file_gib": world * args.c3_gib,
                         "segment_mb": seg_mb, "GBps": round(world * args.c3_gib * GIB / dt / 1e9, 2),
                         "GBps_per_gpu": round(args.c3_gib * GIB / dt / 1e9, 2), "clean_file_no_failures": ok,
-                        "page_cache": "bypassed (O_DIRECT)" if os.environ.get("NVME_STROM_IO") == "direct" else "warm"})
+                        "page_cache": "bypassed (O_DIRECT)" if os.environ.get("NVME_STROM_IO") == "direct" else ("warm, page-locked (zero-copy)" if args.pin else "warm")})
         barrier()
         if rank == 0:
             os.unlink(path)
