@@ -301,9 +301,8 @@ def run_product(args):
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
             return float(t.item())
 
-        h2d_total = sum_over_ranks(h2d_best)
+        h2d_cal = h2d_total = sum_over_ranks(h2d_best)
         source_total = world * GIB / (ms_src * 1e-3) / 1e9
-        xfer_roof = min(h2d_total, source_total)
 
         # ---- the same pass from a tmpfs file: the library page-locks the mapping and the copy engine
         # reads the page cache itself (no CPU copy); reported beside the ext4 headline, every N ----
@@ -337,7 +336,6 @@ def run_product(args):
                 assert shm_totals == e2e_totals
                 tmpfs = {"value": round(world * GIB / (ms_shm * 1e-3) / 1e9, 2), "unit": "GB/s",
                          "ms_per_step": round(ms_shm, 3), "file_dir": shm,
-                         "frac_of_h2d": round(world * GIB / (ms_shm * 1e-3) / 1e9 / h2d_total, 4),
                          "pin_seconds_once": round(max_over_ranks(pin_s), 3),
                          "how": "same steps, file on tmpfs, after nvme_strom_pin_file() page-locked its mapping "
                                 "(once, outside the steps): H2D straight from the page cache, no staging copy"}
@@ -348,6 +346,13 @@ def run_product(args):
                         os.unlink(spath)
                     except OSError:
                         pass
+
+        # the link cannot be slower than a load that was just observed crossing it: the pinned-buffer
+        # calibration varies by ~8% with where its buffer landed (NUMA), so take the larger figure
+        if tmpfs:
+            h2d_total = max(h2d_total, tmpfs["value"])
+            tmpfs["frac_of_h2d"] = round(tmpfs["value"] / h2d_total, 4)
+        xfer_roof = min(h2d_total, source_total)
 
         # ---- correctness witnesses (no oracle here): a clean file has no failures --------
         merged = multigpu.reduce_totals(e2e_totals, dev)
@@ -424,11 +429,11 @@ def run_product(args):
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                          "algorithmic_bytes_per_launch": pages_mine * 8192},
             "clocks": sampler.summary(),
-            "transfer_roofline": {"h2d_GBps": round(h2d_total, 2), "source_GBps": round(source_total, 2),
+            "transfer_roofline": {"h2d_GBps": round(h2d_total, 2), "h2d_calibrated_GBps": round(h2d_cal, 2), "source_GBps": round(source_total, 2),
                                   "bound": "h2d" if h2d_total <= source_total else "source",
                                   "peak": round(xfer_roof, 2), "frac": round(e2e / xfer_roof, 4),
                                   "how": "h2d: 512 MiB pinned->device cudaMemcpyAsync per rank, all ranks at once, "
-                                         "best of 8, summed; source: the same MEMCPY_SSD2GPU "
+                                         "best of 8, summed (h2d_calibrated), or the tmpfs zero-copy load's rate when that was higher; source: the same MEMCPY_SSD2GPU "
                                          "pipeline with the device copy switched off (strom_debug_skip_h2d), all ranks at once"},
         }
         if tmpfs:
