@@ -185,6 +185,7 @@ def run_product(args):
         ncpu = os.cpu_count() or 16
         os.environ.setdefault("NVME_STROM_READERS", str(max(2, min(16, ncpu // world))))
         os.environ.setdefault("NVME_STROM_HOST_READERS", os.environ["NVME_STROM_READERS"])
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")    # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
