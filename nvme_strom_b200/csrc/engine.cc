@@ -1,31 +1,41 @@
 /*
- * engine.cc -- the transfer pipeline: reader threads, pinned double-buffered
- * staging, cudaMemcpyAsync on per-thread copy streams.
+ * engine.cc -- the transfer pipeline: reader threads, a shared ring of pinned
+ * staging slots, cudaMemcpyAsync on the engine's copy stream.
  *
  * Stands where the kernel module builds PRP lists and posts NVMe READs whose
  * DMA lands in GPU BAR1 (kmod/nvme_strom.c:1414-1482 submit_ssd2gpu_memcpy,
  * :1046-1120 __submit_async_read_cmd, :993-1039 completion callback).  User
  * space cannot aim the SSD's DMA engine at the GPU without the out-of-tree
- * module, so each piece goes   file --pread--> pinned slot --H2D--> HBM   and
+ * module, so each piece goes   file --copy--> pinned slot --H2D--> HBM   and
  * the pipeline's job is to keep both halves busy at once:
  *
- *   - one engine per (device, context); N reader threads each own SLOTS
- *     pinned staging slots, one CUDA stream and one event per slot;
- *   - a thread preads piece k+1 into its next slot while the copy of piece k
- *     is still in flight on its stream (double buffering); it only waits on
- *     an event when it needs that slot again or runs out of work;
+ *   - one engine per (device, context): N reader threads, one ring of SLOTS
+ *     pinned slots (4 x 4 MB), one CUDA stream, one event per slot;
+ *   - a piece is one slot.  Readers take 256 KB sub-pieces of the slot being
+ *     filled; whoever finishes the last one queues the copy of the whole slot
+ *     and everybody moves on to the next slot of the ring while it is in
+ *     flight; a slot's event is waited for only when the ring comes round to
+ *     it, or when there is nothing else to do;
+ *   - the ring, not readers x slots, is what the CPU caches must hold, so the
+ *     footprint stays at 16 MB per GPU whatever the reader count (see
+ *     shared_worker and profiles/r01_slot_sweep.txt);
+ *   - page-locked sources (nvme_strom_pin_file) skip the staging: the copy
+ *     engine reads the page cache itself and the slot lends only its event;
  *   - completion is a host-side refcount drop (task_put): MEMCPY_WAIT sleeps
  *     on a futex and never touches CUDA, so it is legal inside a CUDA stream
  *     callback (utils/nvme_test.c:208-223).
  *
- * SSD2RAM pieces have a host destination: pread straight into the caller's
+ * SSD2RAM pieces have a host destination: read straight into the caller's
  * DMA buffer, no staging (kmod/nvme_strom.c:1693-1761).
  *
  * Environment: NVME_STROM_READERS (threads per engine, default min(16, cpus/2):
  * the other half of the cores is left to the caller and the CUDA driver),
- * NVME_STROM_SLOT_KB (staging slot, default 4096), NVME_STROM_SLOTS (per
- * thread, default 2), NVME_STROM_HOST_READERS (SSD2RAM threads, default
- * min(8, cpus)).  Defaults from the sweep in profiles/r01_xfer_sweep.txt.
+ * NVME_STROM_SLOT_KB (staging slot, default 4096), NVME_STROM_SLOTS (ring
+ * length, default 4), NVME_STROM_SUB_KB (what one reader copies at a time,
+ * default 256), NVME_STROM_SPIN_US (spin before sleeping on a busy slot,
+ * default 200), NVME_STROM_HOST_READERS (SSD2RAM threads, default min(8, cpus)),
+ * NVME_STROM_STAGING=private (the first design: slots and a stream per reader,
+ * NVME_STROM_SLOTS default 2 each; kept for comparison).
  */
 #include "strom_internal.h"
 #include <cstring>
@@ -66,8 +76,15 @@ static int gpu_reader_count()
 /* A request smaller than readers x slot would keep most readers idle if it were cut into
  * slot-sized pieces (a 4MB segment = one piece).  Cut it so that every reader gets one,
  * but not below 256KB, where the per-copy cost of the DMA engine starts to show. */
+static bool shared_staging();
 uint32_t engine_piece_for(uint64_t request_bytes)
 {
+	if (shared_staging())
+	{
+		/* every reader works on the same slot, so a piece is simply a slot (or the request) */
+		const uint64_t whole = (request_bytes + 128 * 1024 - 1) & ~(uint64_t)(128 * 1024 - 1);
+		return (uint32_t)std::min<uint64_t>(engine_piece_max(), std::max<uint64_t>(whole, 128 * 1024));
+	}
 	static const int div = env_int("NVME_STROM_PIECE_DIV", 0, 0, 64);   /* 0: one piece per reader */
 	const uint32_t cap = engine_piece_max();
 	uint64_t per = request_bytes / (uint64_t)(div > 0 ? div : gpu_reader_count());
@@ -75,6 +92,15 @@ uint32_t engine_piece_for(uint64_t request_bytes)
 	if (per >= cap)
 		return cap;
 	return (uint32_t)std::max<uint64_t>(per, 256 * 1024);
+}
+
+/* NVME_STROM_STAGING=shared (default): one ring of slots per engine, every slot filled by all
+ * readers together and sent up with one copy on the engine's single stream.  =private: each
+ * reader owns its slots and its stream (the first design; kept for comparison). */
+static bool shared_staging()
+{
+	static const bool v = [] { const char *e = getenv("NVME_STROM_STAGING"); return !(e && !strcmp(e, "private")); }();
+	return v;
 }
 
 static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
@@ -372,8 +398,8 @@ public:
 			for (const Job &j : jobs)
 				queue_.push_back(j);
 		}
-		if (jobs.size() > 1)
-			cv_.notify_all();
+		if (jobs.size() > 1 || (!host_only_ && shared_staging()))
+			cv_.notify_all();                     /* shared staging: every reader helps with one piece */
 		else
 			cv_.notify_one();
 	}
@@ -442,6 +468,11 @@ private:
 		const DriverApi &api = driver_api();
 		const bool bound = (ctx_ && api.ok && api.cuCtxSetCurrent(ctx_) == 0) ||
 					   cudaSetDevice(device_) == cudaSuccess;
+		if (shared_staging())
+		{
+			shared_worker(index, bound);
+			return;
+		}
 		const int n_slots = env_int("NVME_STROM_SLOTS", 2, 2, 16);
 		/* staging is only ever written by the CPU and read by the DMA engine: write-combined
 		 * memory keeps it out of the caches (NVME_STROM_WC=1; off by default) */
@@ -581,9 +612,302 @@ private:
 			retire(s);
 	}
 
+
+	/* ---- shared staging ring ------------------------------------------------------------
+	 * The ring is what the CPU caches have to hold: slots x slot size per GPU (16 MB by default)
+	 * however many readers there are, so the staged bytes are still in cache when the slot is
+	 * written again, and eight engines on one host do not evict each other (profiles/
+	 * r01_slot_sweep.txt: with private slots the footprint was readers x 2 x slot, and the box's
+	 * aggregate rate fell as it grew).  A piece is one slot; readers take 256 KB sub-pieces of the
+	 * slot being filled, whoever finishes the last one sends the whole slot up with a single
+	 * cudaMemcpyAsync on the engine's one stream, so the copy engine sees long back-to-back copies
+	 * whatever the reader count.  Slots are used in ring order; a slot is waited for (its event)
+	 * only by the reader that needs it next, or by an idle reader. */
+	enum { kFree = 0, kPreparing, kFilling, kInFlight, kRetiring };
+	struct Stage {
+		char *buf = nullptr;
+		cudaEvent_t ev = nullptr;
+		int state = kFree;
+		DmaTask *task = nullptr;          /* owner of the copy in flight                   */
+		uint64_t tsc = 0;
+		Job piece{};                      /* what the slot is being filled with            */
+		uint32_t next_off = 0;            /* next sub-piece to hand out                    */
+		uint32_t unfilled = 0;            /* sub-pieces handed out or still to hand out    */
+		long status = 0;                  /* first error among the fillers                 */
+	};
+
+	void retire_stage(Stage &st)
+	{
+		cudaError_t rc = cudaEventSynchronize(st.ev);
+		if (rc != cudaSuccess)
+		{
+			logf(0, "engine(dev=%d): copy failed: %s", device_, cudaGetErrorName(rc));
+			(void)cudaGetLastError();
+		}
+		stats_dma_finished(st.tsc);
+		task_put(st.task, rc == cudaSuccess ? 0 : -EIO);
+		st.task = nullptr;
+	}
+
+	/* send [buf, buf+len) or, for a page-locked source, the page cache itself; 0 or -EIO */
+	int issue_copy(Stage &st, bool from_source)
+	{
+		const Job &j = st.piece;
+		std::lock_guard<std::mutex> g(issue_lock_);       /* copy + its event, not interleaved */
+		cudaError_t cr = cudaSuccess;
+		if (from_source)
+		{
+			/* one copy per registered region: a source range must lie inside one registration */
+			for (uint64_t done = 0; done < j.length && cr == cudaSuccess;)
+			{
+				const uint64_t off = j.file_off + done;
+				const uint64_t room = SourceMap::kRegion - (off % SourceMap::kRegion);
+				const uint64_t n = std::min<uint64_t>(j.length - done, room);
+				cr = cudaMemcpyAsync(j.dst + done, j.src->base + off, n, cudaMemcpyHostToDevice, stream_);
+				done += n;
+			}
+		}
+		else
+			cr = cudaMemcpyAsync(j.dst, st.buf, j.length, cudaMemcpyHostToDevice, stream_);
+		if (cr == cudaSuccess)
+			cr = cudaEventRecord(st.ev, stream_);
+		if (cr != cudaSuccess)
+		{
+			logf(0, "engine(dev=%d): cannot queue a copy: %s", device_, cudaGetErrorName(cr));
+			(void)cudaGetLastError();
+			return -EIO;
+		}
+		return 0;
+	}
+
+	/* A reader that has to wait for a slot waits for a copy to finish, some tens of
+	 * microseconds: waking a sleeping thread takes about as long (longer in a VM), so spin on
+	 * the change counter for a while before going to sleep.  Call with the lock held. */
+	void wait_for_change(std::unique_lock<std::mutex> &g)
+	{
+		static const uint64_t spin_cycles = (uint64_t)env_int("NVME_STROM_SPIN_US", 200, 0, 100000) * 2000;
+		const uint64_t seen = changes_.load(std::memory_order_relaxed);
+		if (spin_cycles)
+		{
+			g.unlock();
+			const uint64_t t0 = rdtsc_now();
+			while (changes_.load(std::memory_order_acquire) == seen && rdtsc_now() - t0 < spin_cycles)
+				__builtin_ia32_pause();
+			g.lock();
+		}
+		if (changes_.load(std::memory_order_relaxed) == seen)
+			cv_.wait(g);
+	}
+	void announce_change()                    /* lock held */
+	{
+		changes_.fetch_add(1, std::memory_order_release);
+		cv_.notify_all();
+	}
+
+	void shared_worker(int index, bool bound)
+	{
+		const uint32_t slot_sz = engine_piece_max();
+		const uint32_t sub_sz = (uint32_t)env_int("NVME_STROM_SUB_KB", 256, 64, 65536) << 10;
+		if (index == 0)
+		{
+			const int n = env_int("NVME_STROM_SLOTS", 4, 2, 64);
+			const unsigned wc_flag = env_int("NVME_STROM_WC", 0, 0, 1) ? cudaHostAllocWriteCombined : 0;
+			std::vector<Stage> ring((size_t)n);
+			bool ok = bound && cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking) == cudaSuccess;
+			for (int i = 0; ok && i < n; i++)
+				ok = cudaHostAlloc((void **)&ring[(size_t)i].buf, slot_sz, cudaHostAllocPortable | wc_flag) == cudaSuccess &&
+					 cudaEventCreateWithFlags(&ring[(size_t)i].ev, cudaEventDisableTiming) == cudaSuccess;
+			if (!ok)
+			{
+				(void)cudaGetLastError();
+				logf(0, "engine(dev=%d): cannot set up staging; failing its jobs", device_);
+			}
+			std::lock_guard<std::mutex> g(lock_);
+			stages_ = std::move(ring);
+			ring_ok_ = ok;
+		}
+		mark_ready();
+
+		std::unique_lock<std::mutex> g(lock_);
+		for (;;)
+		{
+			/* 1. a sub-piece of the slot being filled */
+			if (open_ >= 0)
+			{
+				Stage &o = stages_[(size_t)open_];
+				if (o.state == kPreparing)
+				{
+					wait_for_change(g);
+					continue;
+				}
+				if (o.state == kFilling && o.next_off < o.piece.length)
+				{
+					const uint32_t off = o.next_off;
+					const uint32_t len = std::min(sub_sz, o.piece.length - off);
+					o.next_off += len;
+					g.unlock();
+					Job part = o.piece;
+					part.file_off += off;
+					part.length = len;
+					const long rc = fetch_piece(part, o.buf + off);
+					g.lock();
+					if (rc != 0 && o.status == 0)
+						o.status = rc;
+					if (--o.unfilled > 0)
+						continue;
+					/* the last filler sends the slot up (state stays kFilling meanwhile) */
+					const long status = o.status;
+					g.unlock();
+					const uint64_t t0 = rdtsc_now();
+					long done_rc = status;
+					bool in_flight = false;
+					if (status == 0 && !g_skip_h2d.load(std::memory_order_relaxed))
+					{
+						stats_dma_started();
+						done_rc = issue_copy(o, false);
+						in_flight = done_rc == 0;
+						if (!in_flight)
+							stats_dma_finished(t0);
+						if (stat_info_level() > 0)
+						{
+							const uint64_t t1 = rdtsc_now();
+							g_stats.nr_submit_dma++;
+							g_stats.clk_submit_dma += t1 > t0 ? t1 - t0 : 0;
+						}
+					}
+					if (!in_flight)
+						task_put(o.piece.task, done_rc);  /* failed, or calibration: read, do not copy */
+					g.lock();
+					if (in_flight)
+					{
+						o.task = o.piece.task;
+						o.tsc = t0;
+					}
+					o.state = in_flight ? kInFlight : kFree;
+					announce_change();
+					continue;
+				}
+				open_ = -1;                               /* all handed out */
+			}
+			/* 2. the next piece, into the next slot of the ring */
+			if (!queue_.empty())
+			{
+				if (!ring_ok_)
+				{
+					Job j = queue_.front();
+					queue_.pop_front();
+					g.unlock();
+					task_put(j.task, -EIO);
+					g.lock();
+					continue;
+				}
+				Stage &n = stages_[(size_t)ring_next_];
+				if (n.state != kFree && n.state != kInFlight)
+				{
+					wait_for_change(g);                   /* still being filled or waited for */
+					continue;
+				}
+				const bool was_in_flight = n.state == kInFlight;
+				const int idx = ring_next_;
+				ring_next_ = (ring_next_ + 1) % (int)stages_.size();
+				Job j = queue_.front();
+				queue_.pop_front();
+				n.state = kPreparing;
+				open_ = idx;
+				g.unlock();
+				if (was_in_flight)
+					retire_stage(n);
+				const bool from_source = j.src && !j.direct && !g_skip_h2d.load(std::memory_order_relaxed) &&
+										 j.task->source->region_ready(j.file_off, j.length, j.task->source, device_);
+				if (from_source)
+				{
+					/* page-locked source (tmpfs): the copy engine reads the page cache itself; the
+					 * slot lends only its event */
+					const uint64_t t0 = rdtsc_now();
+					long rc = injected_fault();
+					n.piece = j;
+					if (rc == 0)
+					{
+						stats_dma_started();
+						rc = issue_copy(n, true);
+						if (rc != 0)
+							stats_dma_finished(t0);
+					}
+					if (rc != 0)
+						task_put(j.task, rc);
+					g.lock();
+					if (rc == 0)
+					{
+						n.task = j.task;
+						n.tsc = t0;
+					}
+					n.next_off = j.length;
+					n.unfilled = 0;
+					n.state = rc == 0 ? kInFlight : kFree;
+					if (open_ == idx)
+						open_ = -1;
+					announce_change();
+					continue;
+				}
+				/* staged.  A piece planned for a page-locked source can be longer than a slot
+				 * (calibration mode, a refused registration): the rest goes back to the head of
+				 * the queue with its own reference on the task. */
+				Job rest = j;
+				const bool split = j.length > slot_sz;
+				if (split)
+				{
+					j.length = slot_sz;
+					rest.file_off += slot_sz;
+					rest.dst += slot_sz;
+					rest.length -= slot_sz;
+					task_add_ref(j.task, 1);
+				}
+				g.lock();
+				if (split)
+					queue_.push_front(rest);
+				n.piece = j;
+				n.next_off = 0;
+				n.unfilled = (j.length + sub_sz - 1) / sub_sz;
+				n.status = 0;
+				n.state = kFilling;
+				announce_change();
+				continue;
+			}
+			/* 3. nothing to read: finish what is in flight, oldest first, then sleep */
+			int oldest = -1;
+			for (size_t k = 0; k < stages_.size() && oldest < 0; k++)
+			{
+				const size_t i = ((size_t)ring_next_ + k) % stages_.size();
+				if (stages_[i].state == kInFlight)
+					oldest = (int)i;
+			}
+			if (oldest >= 0)
+			{
+				Stage &o = stages_[(size_t)oldest];
+				o.state = kRetiring;
+				g.unlock();
+				retire_stage(o);
+				g.lock();
+				o.state = kFree;
+				announce_change();
+				continue;
+			}
+			if (stop_)
+				return;
+			cv_.wait(g);
+		}
+	}
+
 	int device_;
 	void *ctx_;
 	bool host_only_;
+	std::vector<Stage> stages_;           /* shared staging ring (GPU engines)     */
+	bool ring_ok_ = false;
+	int ring_next_ = 0;                   /* slot the next piece goes into         */
+	int open_ = -1;                       /* slot whose sub-pieces are handed out  */
+	cudaStream_t stream_ = nullptr;       /* the engine's one copy stream          */
+	std::mutex issue_lock_;
+	std::atomic<uint64_t> changes_{0};    /* bumped on every slot state change     */
 	std::mutex lock_;
 	std::condition_variable cv_;
 	std::deque<Job> queue_;
