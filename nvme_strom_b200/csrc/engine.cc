@@ -28,12 +28,12 @@
  * SSD2RAM pieces have a host destination: read straight into the caller's
  * DMA buffer, no staging (kmod/nvme_strom.c:1693-1761).
  *
- * Environment: NVME_STROM_READERS (threads per engine, default min(16, cpus/2):
- * the other half of the cores is left to the caller and the CUDA driver),
+ * Environment: NVME_STROM_READERS (threads per engine, default min(16, 3/8 of the cpus):
+ * the rest of the cores is left to the caller, the CUDA driver and SSD2RAM),
  * NVME_STROM_SLOT_KB (staging slot, default 4096), NVME_STROM_SLOTS (ring
  * length, default 4), NVME_STROM_SUB_KB (what one reader copies at a time,
- * default 256), NVME_STROM_SPIN_US (spin before sleeping on a busy slot,
- * default 200), NVME_STROM_HOST_READERS (SSD2RAM threads, default min(8, cpus)),
+ * default 256), NVME_STROM_SPIN_US (yield-spin before sleeping on a busy slot,
+ * default 0: no measurable gain), NVME_STROM_HOST_READERS (SSD2RAM threads, default min(8, cpus)),
  * NVME_STROM_STAGING=private (the first design: slots and a stream per reader,
  * NVME_STROM_SLOTS default 2 each; kept for comparison).
  */
@@ -70,7 +70,10 @@ static int gpu_reader_count()
 {
 	int ncpu = (int)std::thread::hardware_concurrency();
 	if (ncpu < 1) ncpu = 8;
-	return env_int("NVME_STROM_READERS", std::max(2, std::min(ncpu / 2, 16)), 1, 256);
+	/* 3/8 of the cores: a single GPU is link-bound from 6 readers on, and the rest is needed by the
+	 * caller, the driver's threads and the SSD2RAM engine (with 8 + 8 readers on 16 cores the
+	 * two-way compare of bench.py lost a fifth of its rate to descheduled readers) */
+	return env_int("NVME_STROM_READERS", std::max(2, std::min(ncpu * 3 / 8, 16)), 1, 256);
 }
 
 /* A request smaller than readers x slot would keep most readers idle if it were cut into
@@ -685,14 +688,14 @@ private:
 	 * the change counter for a while before going to sleep.  Call with the lock held. */
 	void wait_for_change(std::unique_lock<std::mutex> &g)
 	{
-		static const uint64_t spin_cycles = (uint64_t)env_int("NVME_STROM_SPIN_US", 200, 0, 100000) * 2000;
+		static const uint64_t spin_cycles = (uint64_t)env_int("NVME_STROM_SPIN_US", 0, 0, 100000) * 2000;
 		const uint64_t seen = changes_.load(std::memory_order_relaxed);
 		if (spin_cycles)
 		{
 			g.unlock();
 			const uint64_t t0 = rdtsc_now();
 			while (changes_.load(std::memory_order_acquire) == seen && rdtsc_now() - t0 < spin_cycles)
-				__builtin_ia32_pause();
+				sched_yield();                    /* spin only while nobody else wants the core */
 			g.lock();
 		}
 		if (changes_.load(std::memory_order_relaxed) == seen)
