@@ -183,7 +183,9 @@ def run_product(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         ncpu = os.cpu_count() or 16
-        os.environ.setdefault("NVME_STROM_READERS", str(max(2, min(16, ncpu // world))))
+        # readers per GPU: the cores shared out, an eighth held back for the ranks' own threads
+        # (profiles/r01_slot_sweep.txt C: 10 of 24 at 2 GPUs, 7-8 of 32 at 4, 4 of 32 at 8)
+        os.environ.setdefault("NVME_STROM_READERS", str(max(2, min(16, int((ncpu - ncpu // 8) / world + 0.5)))))
         os.environ.setdefault("NVME_STROM_HOST_READERS", os.environ["NVME_STROM_READERS"])
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")    # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
