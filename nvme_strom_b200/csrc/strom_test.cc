@@ -576,6 +576,17 @@ int main(int argc, char *argv[])
 	}
 	if (devices.empty())
 		devices.push_back(0);
+	if (devices.size() > 1)
+	{
+		/* several engines in one process: share the cores out (an eighth kept back), as bench.py
+		 * does for its ranks; one GPU alone keeps the library's default */
+		long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
+		if (ncpu < 1) ncpu = 8;
+		long per = (long)(((double)(ncpu - ncpu / 8) / (double)devices.size()) + 0.5);
+		char buf[16];
+		snprintf(buf, sizeof(buf), "%ld", per < 2 ? 2 : (per > 16 ? 16 : per));
+		setenv("NVME_STROM_READERS", buf, 0);
+	}
 	if (nr_segments < 1 || segment_sz == 0 || segment_sz % BLCKSZ)
 		usage(argv[0]);
 	CUDA_OK(cudaSetDevice(devices[0]));
