@@ -33,9 +33,9 @@
  * NVME_STROM_SLOT_KB (staging slot, default 4096), NVME_STROM_SLOTS (ring
  * length, default 4), NVME_STROM_SUB_KB (what one reader copies at a time,
  * default 256), NVME_STROM_SPIN_US (yield-spin before sleeping on a busy slot,
- * default 0: no measurable gain), NVME_STROM_HOST_READERS (SSD2RAM threads, default min(8, cpus)),
- * NVME_STROM_STAGING=private (the first design: slots and a stream per reader,
- * NVME_STROM_SLOTS default 2 each; kept for comparison).
+ * default 0: no measurable gain), NVME_STROM_HOST_READERS (SSD2RAM threads, default min(8, cpus)).
+ * The first design (two slots and a stream per reader) is in the history; its numbers are
+ * section A of profiles/r01_slot_sweep.txt.
  */
 #include "strom_internal.h"
 #include <cstring>
@@ -76,34 +76,12 @@ static int gpu_reader_count()
 	return env_int("NVME_STROM_READERS", std::max(2, std::min(ncpu * 3 / 8, 16)), 1, 256);
 }
 
-/* A request smaller than readers x slot would keep most readers idle if it were cut into
- * slot-sized pieces (a 4MB segment = one piece).  Cut it so that every reader gets one,
- * but not below 256KB, where the per-copy cost of the DMA engine starts to show. */
-static bool shared_staging();
+/* Every reader works on the same slot, so a piece is simply a slot (or the whole request when
+ * that is smaller); small requests need no special cut to keep the readers busy. */
 uint32_t engine_piece_for(uint64_t request_bytes)
 {
-	if (shared_staging())
-	{
-		/* every reader works on the same slot, so a piece is simply a slot (or the request) */
-		const uint64_t whole = (request_bytes + 128 * 1024 - 1) & ~(uint64_t)(128 * 1024 - 1);
-		return (uint32_t)std::min<uint64_t>(engine_piece_max(), std::max<uint64_t>(whole, 128 * 1024));
-	}
-	static const int div = env_int("NVME_STROM_PIECE_DIV", 0, 0, 64);   /* 0: one piece per reader */
-	const uint32_t cap = engine_piece_max();
-	uint64_t per = request_bytes / (uint64_t)(div > 0 ? div : gpu_reader_count());
-	per &= ~(uint64_t)(128 * 1024 - 1);
-	if (per >= cap)
-		return cap;
-	return (uint32_t)std::max<uint64_t>(per, 256 * 1024);
-}
-
-/* NVME_STROM_STAGING=shared (default): one ring of slots per engine, every slot filled by all
- * readers together and sent up with one copy on the engine's single stream.  =private: each
- * reader owns its slots and its stream (the first design; kept for comparison). */
-static bool shared_staging()
-{
-	static const bool v = [] { const char *e = getenv("NVME_STROM_STAGING"); return !(e && !strcmp(e, "private")); }();
-	return v;
+	const uint64_t whole = (request_bytes + 128 * 1024 - 1) & ~(uint64_t)(128 * 1024 - 1);
+	return (uint32_t)std::min<uint64_t>(engine_piece_max(), std::max<uint64_t>(whole, 128 * 1024));
 }
 
 static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
@@ -401,20 +379,13 @@ public:
 			for (const Job &j : jobs)
 				queue_.push_back(j);
 		}
-		if (jobs.size() > 1 || (!host_only_ && shared_staging()))
-			cv_.notify_all();                     /* shared staging: every reader helps with one piece */
+		if (jobs.size() > 1 || !host_only_)
+			cv_.notify_all();                     /* GPU engine: every reader helps with one piece */
 		else
 			cv_.notify_one();
 	}
 
 private:
-	struct Slot {
-		char *buf = nullptr;
-		cudaEvent_t ev = nullptr;
-		DmaTask *task = nullptr;          /* non-null while a copy is in flight */
-		uint64_t tsc = 0;
-	};
-
 	bool pop(Job *j, bool block)
 	{
 		std::unique_lock<std::mutex> g(lock_);
@@ -425,21 +396,6 @@ private:
 		*j = queue_.front();
 		queue_.pop_front();
 		return true;
-	}
-
-	void retire(Slot &s)
-	{
-		if (!s.task)
-			return;
-		cudaError_t rc = cudaEventSynchronize(s.ev);
-		if (rc != cudaSuccess)
-		{
-			logf(0, "engine(dev=%d): copy failed: %s", device_, cudaGetErrorName(rc));
-			(void)cudaGetLastError();
-		}
-		stats_dma_finished(s.tsc);
-		task_put(s.task, rc == cudaSuccess ? 0 : -EIO);
-		s.task = nullptr;
 	}
 
 	void mark_ready()
@@ -471,150 +427,8 @@ private:
 		const DriverApi &api = driver_api();
 		const bool bound = (ctx_ && api.ok && api.cuCtxSetCurrent(ctx_) == 0) ||
 					   cudaSetDevice(device_) == cudaSuccess;
-		if (shared_staging())
-		{
-			shared_worker(index, bound);
-			return;
-		}
-		const int n_slots = env_int("NVME_STROM_SLOTS", 2, 2, 16);
-		/* staging is only ever written by the CPU and read by the DMA engine: write-combined
-		 * memory keeps it out of the caches (NVME_STROM_WC=1; off by default) */
-		const unsigned wc_flag = env_int("NVME_STROM_WC", 0, 0, 1) ? cudaHostAllocWriteCombined : 0;
-		const uint32_t slot_sz = engine_piece_max();
-		std::vector<Slot> slots((size_t)n_slots);
-		cudaStream_t stream = nullptr;
-		bool ready = bound && cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking) == cudaSuccess;
-		for (int i = 0; ready && i < n_slots; i++)
-		{
-			if (cudaHostAlloc((void **)&slots[i].buf, slot_sz, cudaHostAllocPortable | wc_flag) != cudaSuccess ||
-				cudaEventCreateWithFlags(&slots[i].ev, cudaEventDisableTiming) != cudaSuccess)
-				ready = false;
-		}
-		if (!ready)
-		{
-			(void)cudaGetLastError();
-			logf(0, "engine(dev=%d): cannot set up staging; failing its jobs", device_);
-		}
-		mark_ready();
-
-		int next = 0;
-		Job j;
-		for (;;)
-		{
-			/* nothing queued: finish what is in flight before sleeping */
-			if (!pop(&j, false))
-			{
-				for (Slot &s : slots)
-					retire(s);
-				if (!pop(&j, true))
-					break;
-			}
-			if (!ready)
-			{
-				task_put(j.task, -EIO);
-				continue;
-			}
-			Slot &s = slots[(size_t)next];
-			next = (next + 1) % n_slots;
-			retire(s);                            /* slot's previous copy must be done */
-			const uint64_t t0 = rdtsc_now();
-			/* page-locked source (tmpfs): the copy engine reads the page cache itself */
-			if (j.src && !j.direct && !g_skip_h2d.load(std::memory_order_relaxed) &&
-				j.task->source->region_ready(j.file_off, j.length, j.task->source, device_))
-			{
-				if (int frc = injected_fault())
-				{
-					task_put(j.task, frc);
-					continue;
-				}
-				stats_dma_started();
-				/* one copy per registered region: a source range must lie inside one registration */
-				cudaError_t cr = cudaSuccess;
-				for (uint64_t done = 0; done < j.length && cr == cudaSuccess;)
-				{
-					const uint64_t off = j.file_off + done;
-					const uint64_t room = SourceMap::kRegion - (off % SourceMap::kRegion);
-					const uint64_t n = std::min<uint64_t>(j.length - done, room);
-					cr = cudaMemcpyAsync(j.dst + done, j.src->base + off, n, cudaMemcpyHostToDevice, stream);
-					done += n;
-				}
-				if (cr == cudaSuccess)
-					cr = cudaEventRecord(s.ev, stream);
-				if (cr != cudaSuccess)
-				{
-					logf(0, "engine(dev=%d): copy from page-locked source failed: %s", device_, cudaGetErrorName(cr));
-					(void)cudaGetLastError();
-					stats_dma_finished(t0);
-					task_put(j.task, -EIO);
-				}
-				else
-				{
-					s.task = j.task;
-					s.tsc = t0;
-				}
-				continue;
-			}
-			/* staged path.  A piece planned for a page-locked source can be longer than a slot
-			 * (calibration mode, a refused registration, a range past EOF): feed it through the
-			 * slots in slot-sized parts, each holding its own reference on the task. */
-			Slot *cur = &s;
-			for (uint32_t done = 0; done < j.length;)
-			{
-				const uint32_t n = std::min<uint32_t>(slot_sz, j.length - done);
-				const bool last_part = done + n == j.length;
-				if (!last_part)
-					task_add_ref(j.task, 1);
-				if (done > 0)
-				{
-					cur = &slots[(size_t)next];
-					next = (next + 1) % n_slots;
-					retire(*cur);
-				}
-				Job part = j;
-				part.file_off = j.file_off + done;
-				part.length = n;
-				part.dst = j.dst + done;
-				const uint64_t tp = rdtsc_now();
-				int rc = fetch_piece(part, cur->buf);
-				if (rc == 0 && g_skip_h2d.load(std::memory_order_relaxed))
-				{
-					task_put(j.task, 0);              /* source-rate calibration: read, do not copy */
-					done += n;
-					continue;
-				}
-				if (rc == 0)
-				{
-					stats_dma_started();
-					cudaError_t cr = cudaMemcpyAsync(part.dst, cur->buf, n, cudaMemcpyHostToDevice, stream);
-					if (cr == cudaSuccess)
-						cr = cudaEventRecord(cur->ev, stream);
-					if (cr != cudaSuccess)
-					{
-						(void)cudaGetLastError();
-						stats_dma_finished(tp);
-						rc = -EIO;
-					}
-				}
-				if (stat_info_level() > 0)
-				{
-					const uint64_t t1 = rdtsc_now();
-					g_stats.nr_submit_dma++;
-					g_stats.clk_submit_dma += t1 > tp ? t1 - tp : 0;
-				}
-				if (rc != 0)
-					task_put(j.task, rc);
-				else
-				{
-					cur->task = j.task;
-					cur->tsc = tp;
-				}
-				done += n;
-			}
-		}
-		for (Slot &s : slots)
-			retire(s);
+		shared_worker(index, bound);
 	}
-
 
 	/* ---- shared staging ring ------------------------------------------------------------
 	 * The ring is what the CPU caches have to hold: slots x slot size per GPU (16 MB by default)

@@ -50,8 +50,8 @@ def main():
     from nvme_strom_b200.loader import heapgen_file
     path = os.path.join(d, "slot_sweep.heap")
     heapgen_file(path, 0x5EED0001, n * 131072)
-    shared = os.environ.get("NVME_STROM_STAGING", "shared") != "private"
-    print(f"# {n} GPUs, {os.cpu_count()} cpus, file {path}, {'shared ring' if shared else 'private slots'}", flush=True)
+    shared = True        # (the private-slot engine of sections A of profiles/r01_slot_sweep.txt is gone)
+    print(f"# {n} GPUs, {os.cpu_count()} cpus, file {path}, shared ring", flush=True)
     try:
         for k, cfg in enumerate(configs):
             readers, slot_kb, slots = cfg.split(":")

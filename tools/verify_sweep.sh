@@ -6,6 +6,5 @@ run s2048x8 NVME_STROM_SLOT_KB=2048 NVME_STROM_SLOTS=8
 run r6 NVME_STROM_READERS=6
 run h4 NVME_STROM_HOST_READERS=4
 run r6h6 NVME_STROM_READERS=6 NVME_STROM_HOST_READERS=6
-run private NVME_STROM_STAGING=private
 run sub128 NVME_STROM_SUB_KB=128
 run slots6 NVME_STROM_SLOTS=6
