@@ -262,7 +262,8 @@ print("split", a.nr_ram2gpu, a.nr_ssd2gpu)
 
 @pytest.mark.parametrize("env", [{"NVME_STROM_IO": "direct"}, {"NVME_STROM_SRC": "pread"}, {"NVME_STROM_FIEMAP": "0"},
                                  {"NVME_STROM_READERS": "1", "NVME_STROM_SLOT_KB": "128", "NVME_STROM_SLOTS": "2"},
-                                 {"NVME_STROM_WC": "1", "NVME_STROM_PIECE_DIV": "3"}])
+                                 {"NVME_STROM_WC": "1", "NVME_STROM_SUB_KB": "64", "NVME_STROM_SLOTS": "3"},
+                                 {"NVME_STROM_READERS": "12", "NVME_STROM_SLOT_KB": "512", "NVME_STROM_SPIN_US": "50"}])
 def test_io_modes_land_the_same_bytes(heapfile, env):
     """O_DIRECT, pread, no FIEMAP, a single reader with tiny slots: same bytes, same counters.
     The switches are read once per process, so each mode runs in a child."""
