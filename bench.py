@@ -69,6 +69,8 @@ class ClockSampler:
         self._stop = threading.Event()
         self._thr = None
         try:
+            if os.environ.get("STROM_BENCH_NO_SAMPLER"):      # diagnostic: is the sampler itself in the way?
+                raise RuntimeError("sampler disabled")
             import pynvml
             pynvml.nvmlInit()
             self.nv = pynvml
@@ -239,10 +241,14 @@ def run_product(args):
             for _ in range(max(args.warmup, 3)):
                 scan_step()
         barrier()
-        launches0 = lib.strom_kernel_launch_count()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         sampler.start()
         with torch.cuda.stream(stream):
+            # one more untimed warm-up launch keeps the GPU busy while the timed ones are queued behind
+            # it: without it the ~90 us between the barrier and the first launch reaching an idle
+            # GPU are charged to the K steps (0.173 vs 0.164 ms per step at K = 10, 2 GPUs)
+            scan_step()
+            launches0 = lib.strom_kernel_launch_count()
             ev0.record(stream)
             for _ in range(args.steps):
                 scan_step()
