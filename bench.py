@@ -253,6 +253,10 @@ def run_product(args):
             for _ in range(args.steps):
                 scan_step()
             ev1.record(stream)
+        # drain before the barrier: its NCCL kernel spins on an SM until the peers arrive, and a
+        # persistent 148-block grid that finds one SM taken runs that launch with a straggler
+        # (0.171 instead of 0.164 ms per step at 2 GPUs; profiles/r01_value_leadin.txt)
+        stream.synchronize()
         barrier()
         sampler.stop()
         launches = lib.strom_kernel_launch_count() - launches0
