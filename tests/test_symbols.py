@@ -49,3 +49,45 @@ def test_no_product_source_touches_the_oracle():
             if os.path.isfile(f) and re.search(r"libstrom_oracle|strom_oracle\.h|ora_[a-z_]+\(", open(f, errors="ignore").read()):
                 bad.append(f)
     assert not bad, bad
+
+
+def test_headers_are_plain_c(tmp_path):
+    """the boundary is a C ABI: every public header compiles as C99 and as C++11 on its own,
+    and a C consumer written against it links with nothing but -lnvme_strom"""
+    import subprocess
+    inc = os.path.join(ROOT, "include")
+    for h in sorted(os.listdir(inc)):
+        for lang, std in (("c", "c99"), ("c++", "c++11")):
+            subprocess.run(["gcc", "-x", lang, f"-std={std}", "-Wall", "-Wextra", "-pedantic", "-Werror",
+                            "-I", inc, "-fsyntax-only", "-"], input=f'#include "{h}"\n', text=True, check=True)
+    src = tmp_path / "consumer.c"
+    src.write_text(r'''
+#include <errno.h>
+#include <stdio.h>
+#include <string.h>
+#include "nvme_strom.h"
+#include "strom_scan.h"
+int main(void)
+{
+    StromCmd__StatInfo st;
+    char banner[256];
+    memset(&st, 0, sizeof(st));
+    st.version = 1;
+    if (nvme_strom_ioctl(STROM_IOCTL__STAT_INFO, &st) != 0 && errno != ENODATA)
+        return 1;
+    if (nvme_strom_version(banner, sizeof(banner)) <= 0)
+        return 2;
+    st.version = 7;                                   /* kmod/nvme_strom.c:1993 */
+    if (nvme_strom_ioctl(STROM_IOCTL__STAT_INFO, &st) != -1 || errno != EINVAL)
+        return 3;
+    printf("%s", banner);
+    return 0;
+}
+''')
+    exe = tmp_path / "consumer"
+    libdir = os.path.join(ROOT, "nvme_strom_b200", "lib")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", inc, str(src), "-L", libdir, "-lnvme_strom",
+                    f"-Wl,-rpath,{libdir}", "-o", str(exe)], check=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, (r.returncode, r.stderr)
+    assert r.stdout.startswith("version: ")
