@@ -40,6 +40,7 @@
 #include "strom_internal.h"
 #include <cstring>
 #include <deque>
+#include <immintrin.h>
 #include <map>
 #include <sched.h>
 #include <sys/mman.h>
@@ -108,11 +109,62 @@ static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
 	return 0;
 }
 
+/*
+ * NVME_STROM_COPY selects how a sub-piece leaves the page cache (experiments for hosts whose caches
+ * are the bottleneck, profiles/r01_slot_sweep.txt; default "memcpy"):
+ *   nta      source lines are prefetched non-temporally ahead of the loads, so that page-cache
+ *            bytes, which are read exactly once, do not push the staging ring out of the caches;
+ *   ntstore  as nta, and the staging slot is written with streaming stores (the ring then lives in
+ *            DRAM and its size stops mattering).
+ * Both need AVX2 and 32-byte alignment (sub-pieces are 4 KB aligned on both sides); anything else
+ * falls back to memcpy.
+ */
+static int copy_mode()
+{
+	static const int v = [] {
+		const char *e = getenv("NVME_STROM_COPY");
+		if (!e || !__builtin_cpu_supports("avx2"))
+			return 0;
+		return !strcmp(e, "nta") ? 1 : (!strcmp(e, "ntstore") ? 2 : 0);
+	}();
+	return v;
+}
+
+__attribute__((target("avx2"))) static void copy_lines_avx2(char *dst, const char *src, uint64_t n, bool stream_stores)
+{
+	constexpr uint64_t kAhead = 1024;                     /* bytes of source prefetched ahead */
+	uint64_t i = 0;
+	for (; i + 64 <= n; i += 64)
+	{
+		if (i + kAhead < n)
+			_mm_prefetch(src + i + kAhead, _MM_HINT_NTA);
+		const __m256i a = _mm256_load_si256(reinterpret_cast<const __m256i *>(src + i));
+		const __m256i b = _mm256_load_si256(reinterpret_cast<const __m256i *>(src + i + 32));
+		if (stream_stores)
+		{
+			_mm256_stream_si256(reinterpret_cast<__m256i *>(dst + i), a);
+			_mm256_stream_si256(reinterpret_cast<__m256i *>(dst + i + 32), b);
+		}
+		else
+		{
+			_mm256_store_si256(reinterpret_cast<__m256i *>(dst + i), a);
+			_mm256_store_si256(reinterpret_cast<__m256i *>(dst + i + 32), b);
+		}
+	}
+	if (stream_stores)
+		_mm_sfence();                                     /* before the copy engine is told to read */
+	if (i < n)
+		memcpy(dst + i, src + i, n - i);
+}
+
 /* piece [off, off+len) out of the mapped file; zeros past EOF like read_fully */
 static void copy_from_map(const SourceMap &m, char *dst, uint32_t len, uint64_t off)
 {
 	uint64_t n = off < m.size ? std::min<uint64_t>(len, m.size - off) : 0;
-	if (n)
+	const int mode = copy_mode();
+	if (n && mode && (((uintptr_t)dst | (uintptr_t)(m.base + off)) & 31) == 0)
+		copy_lines_avx2(dst, m.base + off, n, mode == 2);
+	else if (n)
 		memcpy(dst, m.base + off, n);
 	if (n < len)
 		memset(dst + n, 0, len - n);

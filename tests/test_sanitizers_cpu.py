@@ -34,7 +34,8 @@ def test_host_pipeline_under_sanitizer(tmp_path, san):
 
 
 GPU_MODES = [("load", {}), ("load", {"NVME_STROM_SLOTS": "2", "NVME_STROM_SLOT_KB": "128", "NVME_STROM_SUB_KB": "64"}),
-             ("fault", {"NVME_STROM_FAULT_EVERY": "7"}), ("pinned", {"NVME_STROM_SLOT_KB": "1024"})]
+             ("fault", {"NVME_STROM_FAULT_EVERY": "7"}), ("pinned", {"NVME_STROM_SLOT_KB": "1024"}),
+             ("load", {"NVME_STROM_COPY": "nta"}), ("load", {"NVME_STROM_COPY": "ntstore"})]
 
 
 @pytest.mark.parametrize("san", ["thread", "address,undefined"])
