@@ -165,8 +165,13 @@ typedef struct StromCmd__MemCopySsdToRam {
 	uint32_t __user *chunk_ids;   /* in  */
 } StromCmd__MemCopySsdToRam;
 
-/* ALLOC_DMA_BUFFER: a pinned-on-first-use host buffer returned as a file
- * descriptor (memfd) that the caller mmap()s MAP_SHARED and close()s.
+/* ALLOC_DMA_BUFFER: a host buffer returned as a file descriptor (memfd) that
+ * the caller mmap()s MAP_SHARED and close()s (kmod/pmemmap.c:625-717).  With
+ * node_id >= 0 its pages are bound to that NUMA node (shared memory policy on
+ * the memfd, so every mapping of it allocates there).  The library does not
+ * page-lock it for CUDA: MEMCPY_SSD2RAM needs no GPU, and a consumer that
+ * copies the buffer up afterwards registers its own mapping (cudaHostRegister),
+ * as nvme_strom_b200/loader.py and strom_test do.
  * errno: EINVAL (length < 4KB or not a 4KB multiple; node_id out of range) */
 typedef struct StromCmd__AllocDMABuffer {
 	size_t length;                /* in  */

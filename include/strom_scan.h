@@ -68,6 +68,8 @@ typedef struct StromScanTotals { uint64_t v[STROM_T_COUNT]; } StromScanTotals;
 
 /* scan flags */
 #define STROM_SCAN_DEFAULT   0u
+/* kernel-selection bits: honoured by the experiments build only (libnvme_strom_exp.so,
+ * strom_experiments_built() == 1); the shipped library carries one kernel and ignores them */
 #define STROM_SCAN_KERNEL_LDG 0x100u   /* force the register-streaming kernel   */
 #define STROM_SCAN_KERNEL_TMA 0x200u   /* force the bulk-copy (TMA) kernel      */
 
@@ -144,20 +146,24 @@ int strom_verify_pages(unsigned long handle_a, size_t offset_a,
  *    a larger n_pages is refused with -1 / EINVAL and a message in
  *    strom_last_error() -- split the range and merge with strom_totals_merge();
  *  - the array (1 MiB + 256 bytes) is resident on every GPU that loads the
- *    library, until the process exits;
- *  - all calls on one device use the same array.  The counters are cleared at
+ *    library, until the process exits (strictly: once per CUDA context that
+ *    loads it -- a process holding two contexts on one GPU holds two copies,
+ *    and each context is handed the address of its own);
+ *  - all calls in one context use the same array.  The counters are cleared at
  *    the start of every call and every page record up to n_pages is rewritten,
  *    so a call never sees the previous one's values -- but two calls that are
  *    in flight on the same GPU at the same time (two threads, two streams)
  *    overwrite each other: serialise them;
- *  - the first call on each device looks up the device address of the array
- *    (once, with that device current).  Make that first call during start-up,
- *    before any stream capture begins on the device.
+ *  - the first call on each device (in each context) looks up the device
+ *    address of the array, once, with that device current, and loads the
+ *    kernel.  Make that first call during start-up, before any stream capture
+ *    begins on the device.
  *
  * d_pages: device pointer, 16-byte aligned, on the current device.  h_results
  * (may be NULL) and h_totals are HOST pointers; the call returns when they are
- * filled.  Work is ordered on `stream` (NULL = default stream).  Results are
- * identical to strom_scan_pages_dev() / strom_scan_pages().
+ * filled.  Work is ordered on `stream` (NULL = default stream).  The kernel is
+ * the one strom_scan_pages_dev() launches, picked by size the same way, and the
+ * results are identical to strom_scan_pages_dev() / strom_scan_pages().
  */
 #define STROM_STATIC_SCRATCH_MAX_PAGES 131072u
 int strom_scan_pages_static(const void *d_pages, uint64_t n_pages, uint32_t first_blkno,
@@ -182,6 +188,11 @@ const char *strom_last_error(void);
 
 /* how many kernels this library has launched in this process (bench counter) */
 uint64_t strom_kernel_launch_count(void);
+
+/* 1 in libnvme_strom_exp.so (built with -DSTROM_EXPERIMENTS: the page-scan kernels that were
+ * measured and dropped stay selectable there, for the parity tests and the microbenchmarks),
+ * 0 in the shipped library */
+int strom_experiments_built(void);
 
 /* ---- synthetic heap files (SURVEY.md 8d generator; product-side copy so that
  * benchmarks need nothing from oracle/) -------------------------------------- */

@@ -10,6 +10,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libnvme_strom.so")
 PRELOAD_PATH = os.path.join(_HERE, "lib", "libnvme_strom_preload.so")
+EXP_LIB_PATH = os.path.join(_HERE, "lib", "libnvme_strom_exp.so")
 
 
 def load():
@@ -22,3 +23,13 @@ def load():
 
 
 lib = load()
+
+
+def load_experiments():
+    """The experiments build (make exp): the shipped library plus the page-scan kernels that were
+    measured and dropped, selectable with NVME_STROM_SCAN_VARIANT / NVME_STROM_FUSED_R.  Only the
+    parity tests and tools/microbench.py load it; it is a second, independent copy of the library
+    (own handle tables), so use it for the stateless *_dev entry points only."""
+    if not os.path.exists(EXP_LIB_PATH):
+        raise ImportError(f"{EXP_LIB_PATH} is missing: build it with `make -C nvme_strom_b200/csrc exp`")
+    return ctypes.CDLL(EXP_LIB_PATH, use_errno=True)

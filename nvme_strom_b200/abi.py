@@ -123,14 +123,45 @@ lib.nvme_strom_pin_file.argtypes = [C.c_int]
 lib.nvme_strom_pin_file_range.argtypes = [C.c_int, C.c_uint64, C.c_uint64]
 lib.nvme_strom_version.argtypes = [C.c_char_p, C.c_size_t]
 lib.nvme_strom_version.restype = C.c_size_t
-lib.strom_totals_reset_dev.argtypes = [C.c_void_p, C.c_void_p]
-lib.strom_scan_pages_dev.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p,
-                                     C.c_void_p, C.c_void_p]
-lib.strom_verify_pages_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+
+
+def _declare_dev_entry_points(l):
+    l.strom_totals_reset_dev.argtypes = [C.c_void_p, C.c_void_p]
+    l.strom_scan_pages_dev.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p,
                                        C.c_void_p, C.c_void_p]
-lib.strom_scan_verify_pages_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32,
-                                            C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p,
-                                            C.c_void_p]
+    l.strom_verify_pages_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                         C.c_void_p, C.c_void_p]
+    l.strom_scan_verify_pages_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32,
+                                              C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p,
+                                              C.c_void_p]
+    l.strom_last_error.restype = C.c_char_p
+    l.strom_kernel_launch_count.restype = C.c_uint64
+
+
+_declare_dev_entry_points(lib)
+_exp = None
+
+
+def exp_lib():
+    """libnvme_strom_exp.so (kernel experiments), loaded on first use; see _lib.load_experiments"""
+    global _exp
+    if _exp is None:
+        from ._lib import load_experiments
+        _exp = load_experiments()
+        _declare_dev_entry_points(_exp)
+        assert _exp.strom_experiments_built() == 1
+    return _exp
+
+
+def scan_lib(flags=0):
+    """the library a *_dev scan call should go to: the experiments build when a kernel variant is
+    asked for (environment or flags), else the shipped one"""
+    import os
+    if flags or os.environ.get("NVME_STROM_SCAN_VARIANT") or os.environ.get("NVME_STROM_FUSED_R"):
+        return exp_lib()
+    return lib
+
+
 lib.strom_scan_pages.argtypes = [C.c_ulong, C.c_size_t, C.c_uint64, C.c_uint32, C.c_uint32,
                                  C.c_void_p, C.c_void_p]
 lib.strom_verify_pages.argtypes = [C.c_ulong, C.c_size_t, C.c_ulong, C.c_size_t, C.c_uint64,

@@ -17,14 +17,15 @@
 #include <errno.h>
 #include <fcntl.h>
 #include <stdarg.h>
+#include <stdatomic.h>
 #include <string.h>
 #include <sys/types.h>
 #include <unistd.h>
 #include "nvme_strom.h"
 
 #define MAX_FDS 4096
-static int session_of_fd[MAX_FDS];       /* 0 = not ours */
-static off_t read_pos[MAX_FDS];
+static _Atomic int session_of_fd[MAX_FDS];  /* 0 = not ours; read and written from any thread */
+static _Atomic long read_pos[MAX_FDS];
 
 typedef int (*open_fn)(const char *, int, ...);
 typedef int (*ioctl_fn)(int, unsigned long, ...);
@@ -39,10 +40,20 @@ static int open_common(const char *sym, const char *path, int flags, mode_t mode
 	{
 		int fd = real("/dev/null", O_RDONLY | O_CLOEXEC);
 
-		if (fd >= 0 && fd < MAX_FDS)
+		if (fd >= MAX_FDS)
 		{
-			session_of_fd[fd] = nvme_strom_open();
+			/* no room to remember the session: fail the open like a full descriptor table would,
+			 * instead of handing back a descriptor whose ioctls would end in ENOTTY */
+			close_fn real_close = (close_fn)dlsym(RTLD_NEXT, "close");
+
+			real_close(fd);
+			errno = EMFILE;
+			return -1;
+		}
+		if (fd >= 0)
+		{
 			read_pos[fd] = 0;
+			session_of_fd[fd] = nvme_strom_open();
 		}
 		return fd;
 	}
@@ -106,7 +117,7 @@ ssize_t read(int fd, void *buf, size_t len)
 		if (len > n - pos)
 			len = n - pos;
 		memcpy(buf, text + pos, len);
-		read_pos[fd] += (off_t)len;
+		read_pos[fd] += (long)len;
 		return (ssize_t)len;
 	}
 	return real(fd, buf, len);
@@ -116,10 +127,12 @@ int close(int fd)
 {
 	close_fn real = (close_fn)dlsym(RTLD_NEXT, "close");
 
-	if (fd >= 0 && fd < MAX_FDS && session_of_fd[fd] != 0)
+	if (fd >= 0 && fd < MAX_FDS)
 	{
-		nvme_strom_close(session_of_fd[fd]);
-		session_of_fd[fd] = 0;
+		int session = atomic_exchange(&session_of_fd[fd], 0);
+
+		if (session != 0)
+			nvme_strom_close(session);
 	}
 	return real(fd);
 }

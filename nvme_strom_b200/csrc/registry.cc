@@ -56,6 +56,15 @@ const DriverApi &driver_api()
 	return api;
 }
 
+void *current_context()
+{
+	const DriverApi &api = driver_api();
+	void *ctx = nullptr;
+	if (api.ok && api.cuCtxGetCurrent(&ctx) != 0)
+		ctx = nullptr;
+	return ctx;
+}
+
 /* ------------------------------------------------------------------ */
 /* windows                                                             */
 /* ------------------------------------------------------------------ */
@@ -239,6 +248,8 @@ int do_alloc_dma_buffer(StromCmd__AllocDMABuffer *arg)
 		return -EINVAL;
 	if (arg->node_id >= 0 && arg->node_id >= numa_node_count())
 		return -EINVAL;
+	/* the name a consumer sees in /proc/<pid>/maps and fd listings keeps the module's format and
+	 * unit thresholds (kmod/pmemmap.c:677-685) on purpose: visible-format compatibility */
 	char name[80];
 	const unsigned node = (unsigned)arg->node_id;
 	if (arg->length < (8ul << 20))
@@ -256,6 +267,25 @@ int do_alloc_dma_buffer(StromCmd__AllocDMABuffer *arg)
 		close(fd);
 		return -e;
 	}
+	if (arg->node_id >= 0)
+	{
+		/* node-local pages, as the module allocates them (kmod/pmemmap.c:630-674 alloc_pages_node):
+		 * a memory policy set through one shared mapping of a shmem file belongs to the file, so
+		 * binding a transient mapping binds every later mapping the caller makes.  Best effort: a
+		 * kernel without NUMA support leaves the default policy in place. */
+		void *p = mmap(nullptr, arg->length, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+		if (p != MAP_FAILED)
+		{
+			unsigned long mask[16] = {};
+			if (arg->node_id < (int)(sizeof(mask) * 8))
+			{
+				mask[arg->node_id / (8 * sizeof(long))] |= 1ul << (arg->node_id % (8 * sizeof(long)));
+				if (syscall(SYS_mbind, p, arg->length, 2 /* MPOL_BIND */, mask, sizeof(mask) * 8 + 1, 0u) != 0)
+					logf(1, "ALLOC_DMA_BUFFER: mbind to node %d failed (errno %d): default placement", arg->node_id, errno);
+			}
+			munmap(p, arg->length);
+		}
+	}
 	struct stat st;
 	if (fstat(fd, &st) != 0)
 	{
@@ -264,7 +294,16 @@ int do_alloc_dma_buffer(StromCmd__AllocDMABuffer *arg)
 		return -e;
 	}
 	{
+		/* An inode number is handed out again only after its old file is gone for good (last
+		 * mapping and last descriptor), so an older entry with this number is dead: drop it, and
+		 * with it any cached VMA, before the number can lend its old length to the new buffer. */
 		std::lock_guard<std::mutex> g(g_buf_lock);
+		for (size_t i = 0; i < g_buffers.size();)
+			if (g_buffers[i].ino == (uint64_t)st.st_ino && g_buffers[i].dev == (uint64_t)st.st_dev)
+				g_buffers.erase(g_buffers.begin() + (long)i);
+			else
+				i++;
+		g_vma_cache.clear();
 		g_buffers.push_back({(uint64_t)st.st_ino, (uint64_t)st.st_dev, (uint64_t)arg->length, arg->node_id});
 	}
 	arg->dmabuf_fdesc = fd;

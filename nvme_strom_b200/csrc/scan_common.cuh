@@ -129,7 +129,11 @@ DeviceInfo *device_info();
  * in flight, min blocks per SM); default picked by measurement */
 struct Variant { bool tma; int a, b; bool dyn = false; bool col = false; bool ring = false; bool lean = false; bool roll = false; };
 
-/* the experimental kernels (scan_variants.cu): tma:W:S, col:W, roll:D:B */
-int launch_experimental(const Variant &v, DeviceInfo *d, const ScanArgs &a, cudaStream_t st);
+#ifdef STROM_EXPERIMENTS
+/* scan_variants.cu (experiments build only): true when NVME_STROM_SCAN_VARIANT / the flags /
+ * NVME_STROM_FUSED_R select a kernel other than the shipped one; *rc is then its launch's result */
+bool launch_variant_scan(uint32_t flags, DeviceInfo *d, const ScanArgs &a, cudaStream_t st, int *rc);
+bool launch_variant_fused(DeviceInfo *d, const ScanArgs &a, cudaStream_t st, int *rc);
+#endif
 
 } /* namespace strom */

@@ -9,8 +9,10 @@
  * (128 bytes) and, if asked for, 8 bytes per page cross PCIe.
  *
  * The device-side totals block and the per-page result staging are scratch
- * memory owned by the library: one growable allocation per device, guarded by
- * a per-device mutex, on a per-device non-blocking stream.
+ * memory owned by the library: one growable allocation, one non-blocking
+ * stream and one mutex per (device, context) -- a stream or an allocation made
+ * in one context is not valid in another context of the same GPU, and the
+ * window's own context is the one made current for the call.
  */
 #include "strom_internal.h"
 #include "strom_scan.h"
@@ -26,7 +28,7 @@ struct DeviceScratch {
 	void *d_buf = nullptr;                     /* per-page results or block map */
 	size_t d_buf_size = 0;
 };
-static DeviceScratch g_scratch[64];
+static PerContext<DeviceScratch> g_scratch;
 
 static int scratch_prepare(DeviceScratch &s, size_t need)
 {
@@ -73,7 +75,7 @@ extern "C" int strom_scan_pages(unsigned long handle, size_t offset, uint64_t n_
 	int rc = window_span(w, offset, n_pages * (uint64_t)STROM_BLCKSZ, &pages);
 	if (rc == 0 && (rc = window_make_current(*w)) == 0)
 	{
-		DeviceScratch &s = g_scratch[w->device & 63];
+		DeviceScratch &s = g_scratch.get(w->device, current_context());
 		std::lock_guard<std::mutex> g(s.lock);
 		rc = scratch_prepare(s, h_results ? n_pages * sizeof(StromPageResult) : 0);
 		if (rc == 0) rc = strom_totals_reset_dev(s.d_totals, s.stream);
@@ -118,15 +120,15 @@ extern "C" int strom_verify_pages(unsigned long handle_a, size_t offset_a,
 					span_b = (uint64_t)h_map[i] + 1;
 		rc = window_span(wb, offset_b, span_b * (uint64_t)STROM_BLCKSZ, &pb);
 	}
-	if (rc == 0 && wa->device != wb->device)
+	if (rc == 0 && (wa->device != wb->device || wa->ctx != wb->ctx))
 	{
-		set_error("verify: the two windows are on different devices");
+		set_error("verify: the two windows are on different devices or belong to different contexts");
 		errno = EINVAL;
 		rc = -1;
 	}
 	if (rc == 0 && (rc = window_make_current(*wa)) == 0)
 	{
-		DeviceScratch &s = g_scratch[wa->device & 63];
+		DeviceScratch &s = g_scratch.get(wa->device, current_context());
 		std::lock_guard<std::mutex> g(s.lock);
 		rc = scratch_prepare(s, h_map ? n_blocks * sizeof(uint32_t) : 0);
 		if (rc == 0 && h_map && n_blocks &&

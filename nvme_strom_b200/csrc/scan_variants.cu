@@ -2,17 +2,375 @@
  * scan_variants.cu -- page-scan kernels with OTHER mappings than the default,
  * kept selectable (NVME_STROM_SCAN_VARIANT) because they are the evidence for the
  * design choice; every one is bit-exact on the parity suite.  DESIGN.md 4 has the
- * numbers.  Same arithmetic as page_scan.cu (page_math.cuh).
+ * numbers.  Same arithmetic as the shipped kernel (page_math.cuh).  Built only with
+ * -DSTROM_EXPERIMENTS into lib/libnvme_strom_exp.so (tests, tools/microbench.py); the
+ * shipped libnvme_strom.so carries none of this.
  *
+ *  scan_lean_kernel      rows double-buffered in registers, compact code
+ *  scan_ldg_kernel       the first version: same with all 64 rows unrolled (166KB of SASS)
  *  scan_tma_kernel<W,S>  one warp per page, lane j = column j; each warp owns a ring of
  *                        S 8KB shared-memory slots filled by 1-D bulk async copies
  *                        (cp.async.bulk -> UBLKCP) completing on an mbarrier
  *  scan_col_kernel<W>    same mapping, the whole next page requested into registers
  *  scan_roll_kernel<D>   the default mapping with a rolling window of D rows in registers
  */
-#include "scan_common.cuh"
+#include "scan_ring.cuh"
 
 namespace strom {
+
+/* ------------------------------------------------------------------ */
+/* kernel B: kernel C with a small instruction footprint.  Kernel C       */
+/* unrolls all 64 rows with the line-pointer checks inlined in each: 166KB */
+/* of SASS, and ncu shows warps waiting for instructions as often as for  */
+/* memory (stall "no instruction" 3.4 vs "long scoreboard" 3.3 per issue). */
+/* Here only two batches (ping-pong register buffers) are unrolled and the */
+/* line-pointer rules live in one out-of-line function that the few rows   */
+/* holding line pointers call.                                             */
+/* ------------------------------------------------------------------ */
+template <int R, bool VERIFY, int MINB, int THREADS = kLdgThreads>
+__global__ void __launch_bounds__(THREADS, MINB)
+scan_lean_kernel(ScanArgs a)
+{
+	__shared__ unsigned long long s_tot[STROM_T_COUNT];
+	constexpr int NB = 64 / R;
+	static_assert(NB % 2 == 0, "two batches per loop trip");
+	constexpr uint32_t FULL = 0xFFFFFFFFu;
+	constexpr int RV = VERIFY ? R : 1;
+	const uint32_t lane = threadIdx.x & 31, k = lane & 7, gbase = lane & ~7u;
+	/* page numbers fit 32 bits (the launcher refuses more than 2^32 pages = 32 TiB) */
+	const uint32_t n_pages = (uint32_t)a.n_pages;
+	const uint32_t n_groups = (gridDim.x * THREADS) >> 3;
+	uint32_t page = (blockIdx.x * THREADS + threadIdx.x) >> 3;
+	const uint32_t seed0 = kLaneSeed[4 * k], seed1 = kLaneSeed[4 * k + 1],
+				   seed2 = kLaneSeed[4 * k + 2], seed3 = kLaneSeed[4 * k + 3];
+
+	if (threadIdx.x < STROM_T_COUNT)
+		s_tot[threadIdx.x] = (threadIdx.x == STROM_T_FIRST_MISMATCH) ? ~0ull : 0ull;
+	__syncthreads();
+
+	if (page - (lane >> 3) < n_pages)
+	{
+		auto row_ptr = [&](const uint4 *base, uint32_t pg) {
+			return base + (size_t)(pg < n_pages ? pg : n_pages - 1) * 512 + k;
+		};
+		const uint4 *p = row_ptr(a.pages, page);
+		const uint4 *q = VERIFY ? row_ptr(a.ref, page) : nullptr;
+		uint4 bufa[R], bufb[R], refa[RV], refb[RV];
+
+#pragma unroll
+		for (int r = 0; r < R; r++)
+		{
+			bufa[r] = ldg_stream(p + r * 8);
+			if (VERIFY) refa[r] = ldg_stream(q + r * 8);
+		}
+		for (;;)
+		{
+			/* 64-bit overflow-free: n_groups <= 2^20, pages < 2^32 - 2^21 is checked at launch */
+			const uint32_t npage = page + n_groups;
+			const bool more = npage - (lane >> 3) < n_pages;
+			uint32_t s0 = seed0, s1 = seed1, s2 = seed2, s3 = seed3;
+			uint32_t orv = 0, cnt = 0, first_unit = 0xFFFFu;
+			uint32_t hstate = 0, bounds = 0, lp_end = 0;        /* bounds = pd_upper | pd_special << 16 */
+
+			auto compute = [&](const uint4 (&x)[R], const uint4 (&y)[RV], int b, bool first_batch) {
+#pragma unroll
+				for (int r = 0; r < R; r++)
+				{
+					const uint32_t row = (uint32_t)b * R + r;
+					uint4 v = x[r];
+					if (r == 0 && first_batch)
+					{
+						const uint32_t w2 = __shfl_sync(FULL, v.z, gbase);
+						const uint32_t w3 = __shfl_sync(FULL, v.w, gbase);
+						const uint32_t w4 = __shfl_sync(FULL, v.x, gbase + 1);
+						const PageHeader h = decode_header(w2, w3, w4);
+						hstate = pack_header_state(h);
+						bounds = h.upper | (h.special << 16);
+						lp_end = kHdrWords + h.nlp;
+					}
+					orv |= v.x | v.y | v.z | v.w;
+					if (VERIFY)
+					{
+						const uint4 u = y[r];
+						if (((v.x ^ u.x) | (v.y ^ u.y) | (v.z ^ u.z) | (v.w ^ u.w)) != 0)
+							first_unit = min(first_unit, row * 8 + k);
+					}
+					if (row * 32 < lp_end)
+						cnt += lp_check_row(v.x, v.y, v.z, v.w, row * 32 + 4 * k, bounds & 0xFFFFu, bounds >> 16,
+											lp_end - kHdrWords);
+					if (r == 0 && first_batch && k == 0)
+						v.z &= 0xFFFF0000u;
+					s0 = fnv_mix(s0, v.x);
+					s1 = fnv_mix(s1, v.y);
+					s2 = fnv_mix(s2, v.z);
+					s3 = fnv_mix(s3, v.w);
+				}
+			};
+
+#pragma unroll 1
+			for (int b = 0; b < NB; b += 2)
+			{
+#pragma unroll
+				for (int r = 0; r < R; r++)                              /* batch b+1 -> B */
+				{
+					bufb[r] = ldg_stream(p + ((b + 1) * R + r) * 8);
+					if (VERIFY) refb[r] = ldg_stream(q + ((b + 1) * R + r) * 8);
+				}
+				compute(bufa, refa, b, b == 0);
+				const bool last = (b + 2 >= NB);
+				if (!last || more)                                        /* batch b+2, or the next page -> A */
+				{
+					const uint4 *src = last ? row_ptr(a.pages, npage) : p + (b + 2) * R * 8;
+					const uint4 *rsrc = VERIFY ? (last ? row_ptr(a.ref, npage) : q + (b + 2) * R * 8) : nullptr;
+#pragma unroll
+					for (int r = 0; r < R; r++)
+					{
+						bufa[r] = ldg_stream(src + r * 8);
+						if (VERIFY) refa[r] = ldg_stream(rsrc + r * 8);
+					}
+				}
+				compute(bufb, refb, b + 1, false);
+			}
+			uint32_t hash = fnv_mix(fnv_mix(s0, 0), 0) ^ fnv_mix(fnv_mix(s1, 0), 0) ^
+							fnv_mix(fnv_mix(s2, 0), 0) ^ fnv_mix(fnv_mix(s3, 0), 0);
+#pragma unroll
+			for (int d = 4; d >= 1; d >>= 1)
+			{
+				hash ^= __shfl_xor_sync(FULL, hash, d);
+				orv |= __shfl_xor_sync(FULL, orv, d);
+				cnt += __shfl_xor_sync(FULL, cnt, d);
+				if (VERIFY) first_unit = min(first_unit, __shfl_xor_sync(FULL, first_unit, d));
+			}
+			if (k == 0 && page < n_pages)
+			{
+				const StromPageResult r = finish_page(hash, a.first_blkno + page, orv == 0, unpack_header_state(hstate), cnt);
+				if (a.results)
+					a.results[page] = r;
+				tally_page(s_tot, r, VERIFY ? first_unit : 0xFFFFu, a.base_offset + (uint64_t)page * STROM_BLCKSZ);
+			}
+			if (!more)
+				break;
+			page = npage;
+			p = row_ptr(a.pages, page);
+			if (VERIFY) q = row_ptr(a.ref, page);
+		}
+	}
+	publish_totals(s_tot, a.totals);
+}
+
+/* ------------------------------------------------------------------ */
+/* kernel C: register streaming, 8 lanes per page, fully unrolled       */
+/* ------------------------------------------------------------------ */
+template <int R, bool VERIFY, int MINB, bool DYN = false>
+__global__ void __launch_bounds__(kLdgThreads, MINB)
+scan_ldg_kernel(ScanArgs a)
+{
+	__shared__ unsigned long long s_tot[STROM_T_COUNT];
+	constexpr int NB = 64 / R;
+	constexpr uint32_t FULL = 0xFFFFFFFFu;
+	const uint32_t lane = threadIdx.x & 31, k = lane & 7, gbase = lane & ~7u;
+	const uint64_t n_groups = ((uint64_t)gridDim.x * blockDim.x) >> 3;
+	uint64_t page = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+	uint64_t wpage = page - (lane >> 3);                 /* page of the warp's group 0 */
+	const uint32_t seed0 = kLaneSeed[4 * k], seed1 = kLaneSeed[4 * k + 1],
+				   seed2 = kLaneSeed[4 * k + 2], seed3 = kLaneSeed[4 * k + 3];
+	TotalsAcc acc;
+
+	if (wpage < a.n_pages)
+	{
+		/* groups past the end shadow the last page and keep quiet, so that
+		 * the warp-wide shuffles below always see all 32 lanes */
+		bool valid = page < a.n_pages;
+		const uint4 *p = a.pages + (valid ? page : a.n_pages - 1) * 512 + k;
+		const uint4 *q = VERIFY ? a.ref + (valid ? page : a.n_pages - 1) * 512 + k : nullptr;
+		uint4 cur[R], nxt[R], rcur[VERIFY ? R : 1], rnxt[VERIFY ? R : 1];
+
+#pragma unroll
+		for (int r = 0; r < R; r++)
+		{
+			cur[r] = ldg_stream(p + r * 8);
+			if (VERIFY) rcur[r] = ldg_stream(q + r * 8);
+		}
+		for (;;)
+		{
+			uint64_t npage = page + n_groups, nwpage = wpage + n_groups;
+			bool nvalid = npage < a.n_pages, more = nwpage < a.n_pages;
+			const uint4 *np = a.pages + (nvalid ? npage : a.n_pages - 1) * 512 + k;
+			const uint4 *nq = VERIFY ? a.ref + (nvalid ? npage : a.n_pages - 1) * 512 + k : nullptr;
+			unsigned long long ticket = 0;
+			if (DYN && lane == 0)            /* ask early, read late: the atomic's latency is hidden */
+				ticket = atomicAdd(a.tile_counter, 1ull);
+			uint32_t s0 = seed0, s1 = seed1, s2 = seed2, s3 = seed3;
+			uint32_t orv = 0, cnt = 0, first_unit = 0xFFFFu;
+			PageHeader h;
+			uint32_t lp_end = 0;
+
+#pragma unroll
+			for (int b = 0; b < NB; b++)
+			{
+				if (b + 1 < NB)
+				{
+#pragma unroll
+					for (int r = 0; r < R; r++)
+					{
+						nxt[r] = ldg_stream(p + ((b + 1) * R + r) * 8);
+						if (VERIFY) rnxt[r] = ldg_stream(q + ((b + 1) * R + r) * 8);
+					}
+				}
+				else
+				{
+					if (DYN)
+					{
+						ticket = __shfl_sync(FULL, ticket, 0);
+						nwpage = (ticket + (n_groups >> 2)) * 4;
+						npage = nwpage + (lane >> 3);
+						nvalid = npage < a.n_pages;
+						more = nwpage < a.n_pages;
+						np = a.pages + (nvalid ? npage : a.n_pages - 1) * 512 + k;
+						if (VERIFY) nq = a.ref + (nvalid ? npage : a.n_pages - 1) * 512 + k;
+					}
+					if (more)
+					{
+#pragma unroll
+						for (int r = 0; r < R; r++)
+						{
+							nxt[r] = ldg_stream(np + r * 8);
+							if (VERIFY) rnxt[r] = ldg_stream(nq + r * 8);
+						}
+					}
+				}
+				if (b == 0)
+				{
+					const uint32_t w2 = __shfl_sync(FULL, cur[0].z, gbase);
+					const uint32_t w3 = __shfl_sync(FULL, cur[0].w, gbase);
+					const uint32_t w4 = __shfl_sync(FULL, cur[0].x, gbase + 1);
+					h = decode_header(w2, w3, w4);
+					lp_end = kHdrWords + h.nlp;
+				}
+#pragma unroll
+				for (int r = 0; r < R; r++)
+				{
+					const uint32_t row = b * R + r;
+					uint4 v = cur[r];
+					orv |= v.x | v.y | v.z | v.w;
+					if (VERIFY)
+					{
+						const uint4 u = rcur[r];
+						if (((v.x ^ u.x) | (v.y ^ u.y) | (v.z ^ u.z) | (v.w ^ u.w)) != 0)
+							first_unit = min(first_unit, row * 8 + k);
+					}
+					if (row * 32 < lp_end)
+					{
+						const uint32_t widx = row * 32 + 4 * k;
+						if (widx + 0 >= kHdrWords && widx + 0 < lp_end) cnt += lp_check(v.x, h);
+						if (widx + 1 >= kHdrWords && widx + 1 < lp_end) cnt += lp_check(v.y, h);
+						if (widx + 2 >= kHdrWords && widx + 2 < lp_end) cnt += lp_check(v.z, h);
+						if (widx + 3 >= kHdrWords && widx + 3 < lp_end) cnt += lp_check(v.w, h);
+					}
+					if (row == 0 && k == 0)
+						v.z &= 0xFFFF0000u;                            /* pd_checksum := 0 */
+					s0 = fnv_mix(s0, v.x);
+					s1 = fnv_mix(s1, v.y);
+					s2 = fnv_mix(s2, v.z);
+					s3 = fnv_mix(s3, v.w);
+				}
+#pragma unroll
+				for (int r = 0; r < R; r++)
+				{
+					cur[r] = nxt[r];
+					if (VERIFY) rcur[r] = rnxt[r];
+				}
+			}
+			uint32_t hash = fnv_mix(fnv_mix(s0, 0), 0) ^ fnv_mix(fnv_mix(s1, 0), 0) ^
+							fnv_mix(fnv_mix(s2, 0), 0) ^ fnv_mix(fnv_mix(s3, 0), 0);
+#pragma unroll
+			for (int d = 4; d >= 1; d >>= 1)
+			{
+				hash ^= __shfl_xor_sync(FULL, hash, d);
+				orv |= __shfl_xor_sync(FULL, orv, d);
+				cnt += __shfl_xor_sync(FULL, cnt, d);
+				if (VERIFY) first_unit = min(first_unit, __shfl_xor_sync(FULL, first_unit, d));
+			}
+			if (k == 0 && valid)
+			{
+				StromPageResult r = finish_page(hash, a.first_blkno + (uint32_t)page, orv == 0, h, cnt);
+				if (a.results)
+					a.results[page] = r;
+				acc.add(r);
+				if (VERIFY && first_unit != 0xFFFFu)
+				{
+					acc.mismatch++;
+					acc.first = min(acc.first, (unsigned long long)(a.base_offset + page * STROM_BLCKSZ + first_unit * 16));
+				}
+			}
+			if (!more)
+				break;
+			page = npage; wpage = nwpage; valid = nvalid; p = np; q = nq;
+		}
+	}
+	flush_totals(acc, k == 0, s_tot, a.totals);
+}
+
+
+template <int R, bool V, int MINB, bool DYN = false>
+static int launch_ldg(DeviceInfo *d, int slot, const ScanArgs &a_in, cudaStream_t st)
+{
+	ScanArgs a = a_in;
+	if (DYN)
+	{
+		/* experiment: library-owned ticket counter, zeroed in stream order before the launch */
+		static unsigned long long *counter[64];
+		int dv = (int)(d - g_dev);
+		if (!counter[dv])
+			STROM_CUDA_OR_FAIL(cudaMalloc((void **)&counter[dv], 256));
+		STROM_CUDA_OR_FAIL(cudaMemsetAsync(counter[dv], 0, 8, st));
+		a.tile_counter = counter[dv];
+	}
+	static std::atomic<int> occ[64][16];
+	int dev = (int)(d - g_dev);
+	if (occ[dev][slot] == 0)
+	{
+		int n = 0;
+		STROM_CUDA_OR_FAIL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_ldg_kernel<R, V, MINB, DYN>,
+																		 kLdgThreads, 0));
+		occ[dev][slot] = n > 0 ? n : 1;
+	}
+	uint64_t want = (a.n_pages * 8 + kLdgThreads - 1) / kLdgThreads;
+	uint64_t cap = (uint64_t)d->sm_count * occ[dev][slot];
+	int grid = (int)(want < cap ? want : cap);
+	scan_ldg_kernel<R, V, MINB, DYN><<<grid, kLdgThreads, 0, st>>>(a);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	return 0;
+}
+
+template <int R, bool V, int MINB, int THREADS = kLdgThreads>
+static int launch_lean(DeviceInfo *d, const ScanArgs &a, cudaStream_t st)
+{
+	static std::atomic<int> occ[64];
+	int dev = (int)(d - g_dev);
+	if (occ[dev] == 0)
+	{
+		int n = 0;
+		STROM_CUDA_OR_FAIL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_lean_kernel<R, V, MINB, THREADS>,
+																		 THREADS, 0));
+		occ[dev] = n > 0 ? n : 1;
+	}
+	if (a.n_pages >= 0xFFE00000ull)
+	{
+		set_error("scan: more than 2^32 - 2^21 pages in one launch");
+		errno = EINVAL;
+		return -1;
+	}
+	uint64_t want = (a.n_pages * 8 + THREADS - 1) / THREADS;
+	uint64_t cap = (uint64_t)d->sm_count * occ[dev];
+	int grid = (int)(want < cap ? want : cap);
+	scan_lean_kernel<R, V, MINB, THREADS><<<grid, THREADS, 0, st>>>(a);
+	g_kernel_launches++;
+	STROM_CUDA_OR_FAIL(cudaGetLastError());
+	return 0;
+}
+
 
 /* ------------------------------------------------------------------ */
 /* mbarrier / bulk-copy primitives (PTX; SASS: SYNCS.*, UBLKCP)        */
@@ -393,7 +751,7 @@ static int launch_tma(DeviceInfo *d, int slot, const ScanArgs &a, cudaStream_t s
 template <int D, bool V, int MINB, int THREADS = kLdgThreads>
 static int launch_roll(DeviceInfo *d, const ScanArgs &a, cudaStream_t st)
 {
-	static int occ[64];
+	static std::atomic<int> occ[64];
 	int dev = (int)(d - g_dev);
 	if (occ[dev] == 0)
 	{
@@ -429,7 +787,23 @@ static int launch_col(DeviceInfo *d, const ScanArgs &a, cudaStream_t st)
 }
 
 
-int launch_experimental(const Variant &v, DeviceInfo *d, const ScanArgs &a, cudaStream_t st)
+static Variant pick_variant(uint32_t flags)
+{
+	Variant v = {false, 0, 0};      /* a == 0: the measured default, chosen by size below */
+	const char *e = getenv("NVME_STROM_SCAN_VARIANT");
+	if (e && !strncmp(e, "tma:", 4)) { v.tma = true; sscanf(e + 4, "%d:%d", &v.a, &v.b); }
+	else if (e && !strncmp(e, "roll:", 5)) { v.tma = false; v.roll = true; v.a = 16; v.b = 2; sscanf(e + 5, "%d:%d", &v.a, &v.b); }
+	else if (e && !strncmp(e, "lean:", 5)) { v.tma = false; v.lean = true; v.a = 8; v.b = 2; sscanf(e + 5, "%d:%d", &v.a, &v.b); }
+	else if (e && !strncmp(e, "ring:", 5)) { v.tma = false; v.ring = true; v.a = 384; v.b = 32; sscanf(e + 5, "%d:%d", &v.a, &v.b); }
+	else if (e && !strncmp(e, "col:", 4)) { v.tma = false; v.col = true; v.a = atoi(e + 4); }
+	else if (e && !strncmp(e, "ldgdyn", 6)) { v.tma = false; v.a = 8; v.b = 2; v.dyn = true; }
+	else if (e && !strncmp(e, "ldg:", 4)) { v.tma = false; v.a = 8; v.b = 2; sscanf(e + 4, "%d:%d", &v.a, &v.b); }
+	if (flags & STROM_SCAN_KERNEL_LDG) { v = Variant{false, 8, 2}; }
+	if (flags & STROM_SCAN_KERNEL_TMA) { v = Variant{true, 8, 3}; }
+	return v;
+}
+
+static int launch_variant(const Variant &v, DeviceInfo *d, const ScanArgs &a, cudaStream_t st)
 {
 	if (v.tma)
 	{
@@ -463,8 +837,86 @@ int launch_experimental(const Variant &v, DeviceInfo *d, const ScanArgs &a, cuda
 		if (v.a == 4)  return launch_col<4>(d, a, st);
 		return launch_col<12>(d, a, st);
 	}
-	errno = EINVAL;
-	return -1;
+	if (v.lean)
+	{
+		if (v.a == 4 && v.b == 2)  return launch_lean<4, false, 2>(d, a, st);
+		if (v.a == 4 && v.b == 3)  return launch_lean<4, false, 3>(d, a, st);
+		if (v.a == 4 && v.b == 4)  return launch_lean<4, false, 4>(d, a, st);
+		if (v.a == 8 && v.b == 3)  return launch_lean<8, false, 3>(d, a, st);
+		if (v.a == 16 && v.b == 1) return launch_lean<16, false, 1>(d, a, st);
+		if (v.a == 16 && v.b == 2) return launch_lean<16, false, 2>(d, a, st);
+		if (v.a == 8 && v.b == 192) return launch_lean<8, false, 3, 192>(d, a, st);
+		if (v.a == 8 && v.b == 128) return launch_lean<8, false, 5, 128>(d, a, st);
+		if (v.a == 8 && v.b == 160) return launch_lean<8, false, 3, 160>(d, a, st);
+		if (v.a == 8 && v.b == 96)  return launch_lean<8, false, 6, 96>(d, a, st);
+		if (v.a == 8 && v.b == 64)  return launch_lean<8, false, 9, 64>(d, a, st);
+		if (v.a == 4 && v.b == 192) return launch_lean<4, false, 4, 192>(d, a, st);
+		return launch_lean<8, false, 2>(d, a, st);
+	}
+	if (v.ring)
+	{
+		if (v.a == 256 && v.b == 32) return launch_ring<256, 32>(d, 8, a, st);
+		if (v.a == 320 && v.b == 32) return launch_ring<320, 32>(d, 9, a, st);
+		if (v.a == 448 && v.b == 32) return launch_ring<448, 32>(d, 10, a, st);
+		if (v.a == 512 && v.b == 16) return launch_ring<512, 16>(d, 11, a, st);
+		if (v.a == 768 && v.b == 16) return launch_ring<768, 16>(d, 12, a, st);
+		if (v.a == 192 && v.b == 64) return launch_ring<192, 64>(d, 13, a, st);
+		if (v.a == 224 && v.b == 64) return launch_ring<224, 64>(d, 14, a, st);
+		if (v.a == 576 && v.b == 16) return launch_ring<576, 16>(d, 0, a, st);
+		if (v.a == 640 && v.b == 16) return launch_ring<640, 16>(d, 0, a, st);
+		if (v.a == 448 && v.b == 16) return launch_ring<448, 16>(d, 0, a, st);
+		if (v.a == 384 && v.b == 16) return launch_ring<384, 16>(d, 0, a, st);
+		if (v.a == 256 && v.b == 16) return launch_ring<256, 16, 2>(d, 0, a, st);
+		if (v.a == 320 && v.b == 16) return launch_ring<320, 16, 2>(d, 0, a, st);
+		if (v.a == 192 && v.b == 16) return launch_ring<192, 16, 3>(d, 0, a, st);
+		if (v.a == 128 && v.b == 16) return launch_ring<128, 16, 4>(d, 0, a, st);
+		if (v.a == 256 && v.b == 8)  return launch_ring<256, 8, 3>(d, 0, a, st);
+		if (v.a == 512 && v.b == 8)  return launch_ring<512, 8, 2>(d, 0, a, st);
+		return launch_ring<384, 32>(d, 15, a, st);
+	}
+	if (v.dyn)                 return launch_ldg<8, false, 2, true>(d, 7, a, st);
+	if (v.a == 16 && v.b == 1) return launch_ldg<16, false, 1>(d, 8, a, st);
+	if (v.a == 4 && v.b == 1)  return launch_ldg<4, false, 1>(d, 8, a, st);
+	if (v.a == 8 && v.b == 1)  return launch_ldg<8, false, 1>(d, 9, a, st);
+	if (v.a == 4 && v.b == 3)  return launch_ldg<4, false, 3>(d, 10, a, st);
+	if (v.a == 4)  return launch_ldg<4, false, 2>(d, 11, a, st);
+	return launch_ldg<8, false, 2>(d, 12, a, st);
+}
+
+/* true when the environment or the flags ask for a kernel other than the shipped default; *rc
+ * then holds the launch's return code */
+bool launch_variant_scan(uint32_t flags, DeviceInfo *d, const ScanArgs &a, cudaStream_t st, int *rc)
+{
+	const Variant v = pick_variant(flags);
+	if (!v.tma && v.a == 0)
+		return false;
+	*rc = launch_variant(v, d, a, st);
+	return true;
+}
+
+static int launch_fused_variant(DeviceInfo *d, const ScanArgs &a, void *stream)
+{
+	const char *e = getenv("NVME_STROM_FUSED_R");
+	if (atoi(e) == 384)
+		return launch_ring<384, 16, 1, true>(d, 0, a, (cudaStream_t)stream);
+	if (atoi(e) == 192)
+		return launch_ring<192, 16, 2, true>(d, 0, a, (cudaStream_t)stream);
+	if (atoi(e) == 448)
+		return launch_ring<448, 16, 1, true>(d, 0, a, (cudaStream_t)stream);
+	if (e && atoi(e) == 41)
+		return launch_ldg<4, true, 1>(d, 13, a, (cudaStream_t)stream);
+	if (e && atoi(e) == 2)
+		return launch_ldg<2, true, 2>(d, 14, a, (cudaStream_t)stream);
+	return launch_ldg<4, true, 2>(d, 15, a, (cudaStream_t)stream);
+}
+
+bool launch_variant_fused(DeviceInfo *d, const ScanArgs &a, cudaStream_t st, int *rc)
+{
+	const char *e = getenv("NVME_STROM_FUSED_R");
+	if (!e || atoi(e) == 0)
+		return false;
+	*rc = launch_fused_variant(d, a, (void *)st);
+	return true;
 }
 
 } /* namespace strom */

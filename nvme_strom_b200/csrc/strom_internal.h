@@ -178,4 +178,30 @@ struct DriverApi {
 };
 const DriverApi &driver_api();
 
+/* The context current on the calling thread (null when the driver entry points are unavailable or
+ * no context is bound yet).  Streams, allocations, symbol addresses and function attributes belong
+ * to a context, not to a device: a process may hold several contexts on one GPU (the reference's
+ * nvme_test creates its own, utils/nvme_test.c:850, next to any runtime-API user's primary one). */
+void *current_context();
+
+/* Library-owned state that exists once per (device, context). */
+template <class T>
+class PerContext {
+public:
+	/* the entry of (device, ctx), created on first use; entries are never removed */
+	T &get(int device, void *ctx)
+	{
+		std::lock_guard<std::mutex> g(lock_);
+		for (auto &e : items_)
+			if (e->device == device && e->ctx == ctx)
+				return e->value;
+		items_.emplace_back(new Item{device, ctx, T()});
+		return items_.back()->value;
+	}
+private:
+	struct Item { int device; void *ctx; T value; };
+	std::mutex lock_;
+	std::vector<std::unique_ptr<Item>> items_;
+};
+
 } /* namespace strom */

@@ -83,7 +83,7 @@ extern "C" int strom_verify_pages_dev(const void *d_a, const void *d_b, uint64_t
 	}
 	if (n_blocks == 0)
 		return 0;
-	static int sm_count[64], occ[64];
+	static std::atomic<int> sm_count[64], occ[64];   /* facts of the device, the same in every context */
 	int dev = 0;
 	STROM_CUDA_OR_FAIL(cudaGetDevice(&dev));
 	if (dev < 0 || dev >= 64) { errno = EINVAL; return -1; }

@@ -28,7 +28,7 @@ def totals_list(t):
 def scan_dev(pages_dev, n_pages, first_blkno=0, flags=0, want_results=True):
     res = torch.zeros(max(n_pages, 1) * 4, dtype=torch.int16, device="cuda") if want_results else None
     tot = new_totals()
-    abi.check(lib.strom_scan_pages_dev(C.c_void_p(pages_dev.data_ptr()), n_pages, first_blkno & 0xFFFFFFFF,
+    abi.check(abi.scan_lib(flags).strom_scan_pages_dev(C.c_void_p(pages_dev.data_ptr()), n_pages, first_blkno & 0xFFFFFFFF,
                                        flags, C.c_void_p(res.data_ptr()) if want_results else None,
                                        C.c_void_p(tot.data_ptr()), None), "strom_scan_pages_dev")
     out = totals_list(tot)
@@ -39,7 +39,7 @@ def scan_dev(pages_dev, n_pages, first_blkno=0, flags=0, want_results=True):
 def scan_verify_dev(pages_dev, ref_dev, n_pages, first_blkno=0, base_offset=0):
     res = torch.zeros(max(n_pages, 1) * 4, dtype=torch.int16, device="cuda")
     tot = new_totals()
-    abi.check(lib.strom_scan_verify_pages_dev(C.c_void_p(pages_dev.data_ptr()), C.c_void_p(ref_dev.data_ptr()),
+    abi.check(abi.scan_lib().strom_scan_verify_pages_dev(C.c_void_p(pages_dev.data_ptr()), C.c_void_p(ref_dev.data_ptr()),
                                               n_pages, first_blkno & 0xFFFFFFFF, 0, base_offset,
                                               C.c_void_p(res.data_ptr()), C.c_void_p(tot.data_ptr()), None),
               "strom_scan_verify_pages_dev")

@@ -27,6 +27,28 @@ def test_library_exports_every_declared_symbol(strom):
     assert not missing, missing
 
 
+def test_shipped_library_carries_no_experiment_kernels():
+    """ring/verify/extract only in libnvme_strom.so; the measured-and-dropped mappings live in
+    libnvme_strom_exp.so, which exports the same C ABI"""
+    import subprocess
+    libdir = os.path.join(ROOT, "nvme_strom_b200", "lib")
+
+    def kernels(name):
+        out = subprocess.run(["nm", "-C", "--defined-only", os.path.join(libdir, name)], capture_output=True,
+                             text=True, check=True).stdout
+        return {m for m in re.findall(r"strom::(scan_[a-z]+_kernel|verify_blocks_kernel|extract_[a-z]+_kernel)", out)}
+
+    shipped, exp = kernels("libnvme_strom.so"), kernels("libnvme_strom_exp.so")
+    assert "scan_ring_kernel" in shipped and "verify_blocks_kernel" in shipped
+    assert not shipped & {"scan_ldg_kernel", "scan_lean_kernel", "scan_tma_kernel", "scan_col_kernel", "scan_roll_kernel"}
+    assert {"scan_ring_kernel", "scan_ldg_kernel", "scan_lean_kernel", "scan_tma_kernel", "scan_col_kernel",
+            "scan_roll_kernel"} <= exp
+    a = C.CDLL(os.path.join(libdir, "libnvme_strom.so"))
+    b = C.CDLL(os.path.join(libdir, "libnvme_strom_exp.so"))
+    assert a.strom_experiments_built() == 0 and b.strom_experiments_built() == 1
+    assert not [n for n in sorted(declared_functions()) if not hasattr(b, n)]
+
+
 def test_preload_shim_builds_and_links():
     shim = os.path.join(ROOT, "nvme_strom_b200", "lib", "libnvme_strom_preload.so")
     assert os.path.exists(shim)

@@ -48,6 +48,9 @@ def test_two_calls_in_a_row_match_the_existing_entry_points(oracle):
         want_res, want_tot = scan_dev(dev_buf, n, first)              # strom_scan_pages_dev
         assert (got_res == want_res).all()
         assert got_tot == want_tot
+        # the CPU oracle as well, so that this file stands on its own
+        ora_res, ora_tot = oracle.scan(dev_buf.cpu().numpy(), first)
+        assert (got_res == ora_res).all() and got_tot == ora_tot
         # and the allocating handle-level call, which is the one this variant stands in for
         m = map_gpu(dev_buf)
         res2 = np.zeros((n, 4), dtype=np.uint16)
@@ -62,6 +65,34 @@ def test_two_calls_in_a_row_match_the_existing_entry_points(oracle):
     _, empty = scan_static(abi, a, 0, 0)
     assert empty[:11] == [0] * 11 and empty[abi.T_FIRST_MISMATCH] == 2 ** 64 - 1
     del torch
+
+
+def test_device_memory_is_untouched_by_the_calls(oracle):
+    """The one property this entry point exists for: after its first call on the device (set-up:
+    symbol address, kernel load) no call changes the amount of free device memory, whatever the
+    size of the request -- small, large, with and without per-page records, growing and shrinking.
+    cudaMemGetInfo is read straight from the runtime so that torch's own caching cannot hide an
+    allocation made by the library."""
+    import torch
+    from nvme_strom_b200 import abi
+    buf = torch.from_numpy(oracle.gen_pages(0x5EED0001, 0, 4096, mixed=True)).cuda().repeat(8)   # 32768 pages
+    host = buf[:4096 * 8192].cpu().numpy()
+    _, want_small = oracle.scan(host[:100 * 8192], 7)
+    scan_static(abi, buf, 1, 0)                                   # first call: set-up happens here
+    scan_static(abi, buf, 32768, 0)                               # and the long-launch kernel gets loaded
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    for n, want_results in ((100, True), (32768, True), (3, False), (20000, True), (32768, False), (100, True)):
+        _, tot = scan_static(abi, buf, n, 7, want_results=want_results)
+        assert torch.cuda.mem_get_info()[0] == free0, (n, want_results)
+    assert tot == want_small
+    # the allocating entry point, for contrast, does take device memory for a request it has not seen
+    from gpu_util import map_gpu, unmap_gpu
+    m = map_gpu(buf)
+    res = np.zeros((32768, 4), dtype=np.uint16)
+    t = abi.StromScanTotals()
+    abi.check(abi.lib.strom_scan_pages(m.handle, 0, 32768, 0, 0, res.ctypes.data, C.byref(t)), "scan")
+    unmap_gpu(m.handle)
 
 
 def test_limit_is_enforced_with_a_clear_error(oracle):

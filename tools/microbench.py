@@ -62,7 +62,7 @@ def main():
     rows = []
     for v in variants:
         os.environ["NVME_STROM_SCAN_VARIANT"] = v
-        fn = lambda: abi.check(lib.strom_scan_pages_dev(pb, n_pages, 0, 0, pr, pt, None), "scan")
+        fn = lambda: abi.check(abi.scan_lib().strom_scan_pages_dev(pb, n_pages, 0, 0, pr, pt, None), "scan")
         best, med = timed(fn, reps)
         rows.append((v, nbytes / best / 1e6, nbytes / med / 1e6))
         print(f"scan {v:10s}           best {rows[-1][1]:8.1f} GB/s  median {rows[-1][2]:8.1f}  frac {rows[-1][2] / peak:.3f}")
@@ -71,13 +71,13 @@ def main():
     print(f"verify (2 buffers)        best {2 * nbytes / best / 1e6:8.1f} GB/s  median {2 * nbytes / med / 1e6:8.1f}  frac {2 * nbytes / med / 1e6 / peak:.3f}")
     for r in ("0", "384", "192", "448", "4"):
         os.environ["NVME_STROM_FUSED_R"] = r
-        best, med = timed(lambda: abi.check(lib.strom_scan_verify_pages_dev(pb, pf, n_pages, 0, 0, 0, pr, pt, None), "f"), reps)
+        best, med = timed(lambda: abi.check(abi.scan_lib().strom_scan_verify_pages_dev(pb, pf, n_pages, 0, 0, 0, pr, pt, None), "f"), reps)
         print(f"fused scan+verify R={r:3s}   best {2 * nbytes / best / 1e6:8.1f} GB/s  median {2 * nbytes / med / 1e6:8.1f}  frac {2 * nbytes / med / 1e6 / peak:.3f}")
     # small launches: one 32MB segment (what the pipeline launches per slot)
     seg_pages = 4096
     for v in ("ring:256:16", "ring:512:16", "ldg:8:2"):
         os.environ["NVME_STROM_SCAN_VARIANT"] = v
-        best, med = timed(lambda: abi.check(lib.strom_scan_pages_dev(pb, seg_pages, 0, 0, pr, pt, None), "s"), reps)
+        best, med = timed(lambda: abi.check(abi.scan_lib().strom_scan_pages_dev(pb, seg_pages, 0, 0, pr, pt, None), "s"), reps)
         print(f"scan {v:10s} 32MB seg   best {best * 1e3:7.1f} us  median {med * 1e3:7.1f} us  ({seg_pages * 8192 / med / 1e6:.0f} GB/s, L2-resident)")
 
 

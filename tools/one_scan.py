@@ -22,6 +22,6 @@ for i in range(base_pages):
 buf = torch.from_numpy(host).cuda().repeat(mib // 64)
 tot = torch.zeros(abi.T_COUNT, dtype=torch.int64, device="cuda")
 for _ in range(reps):
-    abi.check(lib.strom_scan_pages_dev(C.c_void_p(buf.data_ptr()), mib * 128, 0, 0, None, C.c_void_p(tot.data_ptr()), None), "scan")
+    abi.check(abi.scan_lib().strom_scan_pages_dev(C.c_void_p(buf.data_ptr()), mib * 128, 0, 0, None, C.c_void_p(tot.data_ptr()), None), "scan")
 torch.cuda.synchronize()
 print(variant, tot.cpu().tolist()[:3])

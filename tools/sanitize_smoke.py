@@ -26,14 +26,14 @@ ref = None
 for v in ("ldg:8:2", "ldg:4:3", "ldgdyn", "col:12", "col:8", "tma:8:3", "tma:16:1", "tma:12:2"):
     os.environ["NVME_STROM_SCAN_VARIANT"] = v
     abi.check(lib.strom_totals_reset_dev(pt, None), "reset")
-    abi.check(lib.strom_scan_pages_dev(pa, n, 0, 0, pr, pt, None), v)
+    abi.check(abi.scan_lib().strom_scan_pages_dev(pa, n, 0, 0, pr, pt, None), v)
     torch.cuda.synchronize()
     t = tot.cpu().tolist()
     ref = ref or t
     assert t == ref, v
 os.environ.pop("NVME_STROM_SCAN_VARIANT")
 abi.check(lib.strom_verify_pages_dev(pa, pb, n, None, 0, pt, None), "verify")
-abi.check(lib.strom_scan_verify_pages_dev(pa, pb, n, 0, 0, 0, pr, pt, None), "fused")
+abi.check(abi.scan_lib().strom_scan_verify_pages_dev(pa, pb, n, 0, 0, 0, pr, pt, None), "fused")
 items = torch.zeros(n * 2042 * 3, dtype=torch.int32, device="cuda")
 offs = torch.zeros(n + 1, dtype=torch.int64, device="cuda")
 cnt = torch.zeros(1, dtype=torch.int64, device="cuda")

@@ -27,7 +27,7 @@ def main():
     for v in variants:
         os.environ["NVME_STROM_SCAN_VARIANT"] = v
         abi.check(lib.strom_totals_reset_dev(pt, None), "r")
-        abi.check(lib.strom_scan_pages_dev(C.c_void_p(big.data_ptr()), 131072, 0, 0, None, pt, None), "s")
+        abi.check(abi.scan_lib().strom_scan_pages_dev(C.c_void_p(big.data_ptr()), 131072, 0, 0, None, pt, None), "s")
         torch.cuda.synchronize()
         t = tot.cpu().tolist()
         if ref_tot is None:
@@ -37,12 +37,12 @@ def main():
             n_pages = mib * 128
             k = max(10, min(200, 8192 // mib))
             for _ in range(3):
-                lib.strom_scan_pages_dev(C.c_void_p(big.data_ptr()), n_pages, 0, 0, None, pt, None)
+                abi.scan_lib().strom_scan_pages_dev(C.c_void_p(big.data_ptr()), n_pages, 0, 0, None, pt, None)
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             for _ in range(k):
-                lib.strom_scan_pages_dev(C.c_void_p(big.data_ptr()), n_pages, 0, 0, None, pt, None)
+                abi.scan_lib().strom_scan_pages_dev(C.c_void_p(big.data_ptr()), n_pages, 0, 0, None, pt, None)
             b.record()
             torch.cuda.synchronize()
             us = a.elapsed_time(b) / k * 1e3
