@@ -64,8 +64,9 @@ def bench_dir(need_bytes):
 # clocks: NVML sampler thread running during the timed regions
 # ---------------------------------------------------------------------------
 class ClockSampler:
-    def __init__(self, index):
+    def __init__(self, index, period_s=0.002):
         self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.period_s = period_s
         self._stop = threading.Event()
         self._thr = None
         try:
@@ -94,7 +95,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.002)
+            time.sleep(self.period_s)
 
     def start(self):
         if self.nv:
@@ -116,42 +117,47 @@ class ClockSampler:
 # ---------------------------------------------------------------------------
 # CPU arm: the reference's host path, restated (oracle/) -- rank 0 only
 # ---------------------------------------------------------------------------
-def cpu_path(path, max_bytes, threads, passes, do_compare=False):
-    """returns (GB/s over `passes` passes, phase seconds of the last pass)"""
+def _oracle():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from conftest import Oracle            # bench.py's CPU legs may use the oracle
-    o = Oracle()
+    return Oracle()
+
+
+def cpu_path(path, max_bytes, threads, passes, do_compare=False):
+    """The reference's CPU path over `passes` passes: worker threads and their 32 MB buffers are set
+    up once, before the timer (as the reference allocates at start-up).  Returns (GB/s, per-pass
+    phase seconds averaged over the workers, totals of the last pass)."""
+    o = _oracle()
     secs = (C.c_double * 4)()
     tot = o.Totals()
-    done, wall = 0, 0.0
-    for _ in range(passes):
-        rc = o.lib.ora_cpu_path(path.encode(), SEG, max_bytes, threads, 1, int(do_compare), C.byref(tot), secs)
-        if rc != 0:
-            raise RuntimeError(f"ora_cpu_path failed: {rc}")
-        done += (max_bytes // SEG) * SEG
-        wall += secs[3]
-    return done / wall / 1e9, {"read_s": secs[0], "scan_s": secs[1], "compare_s": secs[2], "wall_s": secs[3]}, \
+    rc = o.lib.ora_cpu_path_passes(path.encode(), SEG, max_bytes, threads, 1, int(do_compare), passes, C.byref(tot), secs)
+    if rc != 0:
+        raise RuntimeError(f"ora_cpu_path_passes failed: {rc}")
+    done = (max_bytes // SEG) * SEG
+    return done / secs[3] / 1e9, {"read_s": secs[0], "scan_s": secs[1], "compare_s": secs[2], "wall_s": secs[3]}, \
         [int(x) for x in tot.v]
 
 
 def run_reference(args):
+    """The reference arm: the reference's CPU path (oracle port) on all host cores.  Nothing of the
+    product runs in this process -- the file comes from the oracle's own generator."""
     rank, _, world = env_rank()
     if rank != 0:
         return 0
-    from nvme_strom_b200.loader import heapgen_file
-    threads = os.cpu_count() or 1
+    threads = len(os.sched_getaffinity(0)) or 1
     nbytes = max(1, args.gpus) * GIB            # the whole job of the GPU arm at this N
     path = os.path.join(bench_dir(nbytes), f"strom_bench_ref_{os.getpid()}.heap")
-    heapgen_file(path, SEED, nbytes // 8192)
+    o = _oracle()
+    if o.lib.ora_gen_file(path.encode(), SEED, nbytes // 8192, 0) != 0:
+        raise RuntimeError("ora_gen_file failed")
     try:
-        for _ in range(args.warmup):
-            cpu_path(path, nbytes, threads, 1)
+        cpu_path(path, nbytes, threads, max(1, args.warmup))
         t0 = time.perf_counter()
-        for _ in range(args.steps):
-            gbps, phases, totals = cpu_path(path, nbytes, threads, 1)
-        dt = (time.perf_counter() - t0) / args.steps
+        gbps, phases, totals = cpu_path(path, nbytes, threads, args.steps)
+        dt_wall = (time.perf_counter() - t0) / args.steps      # includes thread and buffer set-up
     finally:
         os.unlink(path)
+    dt = phases["wall_s"]
     val = nbytes / dt / 1e9
     line = {"impl": "reference", "metric": METRIC, "value": round(val, 3), "unit": "GB/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -160,7 +166,10 @@ def run_reference(args):
             "config": {"workload": f"C1/C2 CPU path: read() of a {max(1, args.gpus)} GiB synthetic heap file in 32 MB pieces "
                                    "into RAM + checksum/validate of every page, all host threads; one step = one pass"},
             "cpu_baseline": {"value": round(val, 3), "unit": "GB/s", "cores": threads, "kind": "port",
-                             "sample": f"{max(1, args.gpus)} GiB per step (the GPU arm's whole job at this N), warm page cache"},
+                             "sample": f"{max(1, args.gpus)} GiB per step (the GPU arm's whole job at this N), warm page cache; "
+                                       "worker threads and buffers set up once outside the timed passes",
+                             "phases_per_pass_s": {k: round(v, 4) for k, v in phases.items()},
+                             "ms_per_step_with_setup": round(dt_wall * 1e3, 3)},
             "e2e": {"value": round(val, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -183,12 +192,13 @@ def run_product(args):
         raise SystemExit("bench.py needs a CUDA device: libnvme_strom has no CPU path for the page kernels")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    cpus_mine = sorted(os.sched_getaffinity(0))
     if world > 1:
-        ncpu = os.cpu_count() or 16
-        # readers per GPU: the cores shared out, an eighth held back for the ranks' own threads
-        # (profiles/r01_slot_sweep.txt C: 10 of 24 at 2 GPUs, 7-8 of 32 at 4, 4 of 32 at 8)
-        os.environ.setdefault("NVME_STROM_READERS", str(max(2, min(16, int((ncpu - ncpu // 8) / world + 0.5)))))
-        os.environ.setdefault("NVME_STROM_HOST_READERS", os.environ["NVME_STROM_READERS"])
+        # every rank keeps to its share of the cores (next to its GPU where the platform says which
+        # those are); the engine counts what it is allowed on and sizes readers and ring by that
+        cpus_mine = multigpu.rank_cpus(local_rank, int(os.environ.get("LOCAL_WORLD_SIZE", world)))
+        if not os.environ.get("STROM_BENCH_NO_AFFINITY"):
+            os.sched_setaffinity(0, cpus_mine)
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")    # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
@@ -216,7 +226,7 @@ def run_product(args):
     barrier()
     shard_bytes = pages_mine * 8192
 
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, 0.002 if world == 1 else 0.05)
     result = {}
     try:
         # ---- (1) HBM-resident scan --------------------------------------------------
@@ -280,9 +290,20 @@ def run_product(args):
         ms_e2e = max_over_ranks(t_local * 1e3)
         e2e = world * GIB / (ms_e2e * 1e-3) / 1e9
 
-        # ---- transfer roofline, calibrated in the same run: min(H2D link, source read rate) ----
+        # ---- transfer roofline, calibrated in the same run: min(H2D link, page-cache read rate) ----
+        def gather(x):
+            if world == 1:
+                return [x]
+            t = torch.tensor([x], dtype=torch.float64, device=dev)
+            out = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(out, t)
+            return [float(o.item()) for o in out]
+
+        # (a) the link: 512 MiB pinned -> device per rank, all ranks at once.  A trial's aggregate is
+        # all bytes over the slowest rank's time; the best trial counts (not a sum of per-rank bests,
+        # which no single moment ever saw)
         host = torch.empty(GIB // 2, dtype=torch.uint8).pin_memory()
-        h2d_best = 0.0
+        h2d_cal, h2d_per_rank = 0.0, []
         for _ in range(8):
             barrier()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -290,10 +311,34 @@ def run_product(args):
             resident[:GIB // 2].copy_(host, non_blocking=True)
             b.record()
             torch.cuda.synchronize()
-            h2d_best = max(h2d_best, (GIB // 2) / (a.elapsed_time(b) * 1e-3) / 1e9)
+            times = gather(a.elapsed_time(b) * 1e-3)
+            agg = world * (GIB // 2) / max(times) / 1e9
+            if agg > h2d_cal:
+                h2d_cal, h2d_per_rank = agg, [round((GIB // 2) / t / 1e9, 2) for t in times]
         del host
+        h2d_total = h2d_cal
+
+        # (b) the source: page-cache read rate of the same file range, by the same number of threads
+        # an engine may use, into cache-resident scratch -- no staging ring, no device, so it does
+        # not move with the staging geometry (all ranks at once, best of 3 passes)
+        est = abi.engine_state(local_rank)
+        fd_src = os.open(path, os.O_RDONLY)
+        pc_best = 0.0
+        try:
+            for _ in range(3):
+                barrier()
+                t0 = time.perf_counter()
+                abi.pagecache_read_GBps(fd_src, first_page * 8192, shard_bytes, est["readers_max"])
+                times = gather(time.perf_counter() - t0)
+                pc_best = max(pc_best, world * shard_bytes / max(times) / 1e9)
+        finally:
+            os.close(fd_src)
+        source_total = pc_best
+
+        # (c) diagnosis only: the MEMCPY_SSD2GPU pipeline with the device copy switched off (moves
+        # with the ring geometry; it is the pipeline's own source side, not a roofline)
         pipe.scan = False
-        lib.strom_debug_skip_h2d(1)                     # same engine, same threads and slots, no H2D
+        lib.strom_debug_skip_h2d(1)
         try:
             pipe.run(path, first_seg, n_seg)
             barrier()
@@ -305,17 +350,7 @@ def run_product(args):
         finally:
             lib.strom_debug_skip_h2d(0)
         pipe.scan = True
-        ms_src = max_over_ranks(src_local * 1e3)
-
-        def sum_over_ranks(x):
-            if world == 1:
-                return x
-            t = torch.tensor([x], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.SUM)
-            return float(t.item())
-
-        h2d_cal = h2d_total = sum_over_ranks(h2d_best)
-        source_total = world * GIB / (ms_src * 1e-3) / 1e9
+        pipeline_source_total = world * GIB / (max_over_ranks(src_local * 1e3) * 1e-3) / 1e9
 
         # ---- the same pass from a tmpfs file: the library page-locks the mapping and the copy engine
         # reads the page cache itself (no CPU copy); reported beside the ext4 headline, every N ----
@@ -366,6 +401,36 @@ def run_product(args):
             h2d_total = max(h2d_total, tmpfs["value"])
             tmpfs["frac_of_h2d"] = round(tmpfs["value"] / h2d_total, 4)
         xfer_roof = min(h2d_total, source_total)
+
+        # ---- config C5, untimed: 1 GiB of mixed-validity pages per rank (same seed, corrupted headers,
+        # checksums and line pointers injected), loaded and scanned through the same pipeline; the
+        # merged counters must equal the committed expectation for this many GiB, integer for integer
+        c5 = None
+        if not args.no_c5:
+            c5_path = path + ".c5"
+            heapgen_file(c5_path, SEED, pages_mine, mixed=True, first_page=first_page, n_threads=len(cpus_mine))
+            barrier()
+            try:
+                c5_totals, _ = pipe.run(c5_path, first_seg, n_seg)
+                c5_merged = multigpu.reduce_totals(c5_totals, dev)
+            finally:
+                barrier()
+                if rank == 0:
+                    try:
+                        os.unlink(c5_path)
+                    except OSError:
+                        pass
+            with open(os.path.join(ROOT, "tests", "golden", "c5_expected_totals.json")) as f:
+                gold = json.load(f)
+            want = gold["totals_by_gib"].get(str(world))
+            c5 = {"bit_exact": (c5_merged == want) if want is not None else None,
+                  "counters": dict(zip(gold["fields"], c5_merged)),
+                  "expected_from": "tests/golden/c5_expected_totals.json (CPU oracle over the same file)"
+                                   if want is not None else f"no committed expectation for {world} GiB"}
+            if want is not None and c5_merged != want:
+                print(json.dumps({"error": "C5 counters differ from the committed expectation",
+                                  "got": c5_merged, "want": want}), file=sys.stderr)
+                raise SystemExit(3)
 
         # ---- correctness witnesses (no oracle here): a clean file has no failures --------
         merged = multigpu.reduce_totals(e2e_totals, dev)
@@ -432,7 +497,8 @@ def run_product(args):
                                    "32 MB segments x 6 slots, checksum + header + line-pointer scan",
                        "file_dir": d, "page_cache": "warm", "l2": "input (1 GiB) >> L2 (126 MB), no flush needed",
                        "parallelism": f"{world} x independent shard, counters merged once",
-                       "readers": os.environ.get("NVME_STROM_READERS", "default")},
+                       "readers": os.environ.get("NVME_STROM_READERS", "self-adjusting"),
+                       "cpus_per_rank": len(cpus_mine)},
             "e2e": {"value": round(e2e, 2), "unit": "GB/s", "ms_per_step": round(ms_e2e, 3),
                     "h2d_bytes_per_step": int(counters["h2d_bytes"]) * world,
                     "d2h_bytes_per_step": int(counters["d2h_bytes"]) * world},
@@ -442,13 +508,24 @@ def run_product(args):
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                          "algorithmic_bytes_per_launch": pages_mine * 8192},
             "clocks": sampler.summary(),
-            "transfer_roofline": {"h2d_GBps": round(h2d_total, 2), "h2d_calibrated_GBps": round(h2d_cal, 2), "source_GBps": round(source_total, 2),
+            "transfer_roofline": {"h2d_GBps": round(h2d_total, 2), "h2d_calibrated_GBps": round(h2d_cal, 2),
+                                  "h2d_per_rank_GBps": h2d_per_rank,
+                                  "page_cache_read_GBps": round(source_total, 2), "source_GBps": round(source_total, 2),
+                                  "pipeline_source_GBps": round(pipeline_source_total, 2),
                                   "bound": "h2d" if h2d_total <= source_total else "source",
                                   "peak": round(xfer_roof, 2), "frac": round(e2e / xfer_roof, 4),
-                                  "how": "h2d: 512 MiB pinned->device cudaMemcpyAsync per rank, all ranks at once, "
-                                         "best of 8, summed (h2d_calibrated), or the tmpfs zero-copy load's rate when that was higher; source: the same MEMCPY_SSD2GPU "
-                                         "pipeline with the device copy switched off (strom_debug_skip_h2d), all ranks at once"},
+                                  "frac_of_h2d": round(e2e / h2d_total, 4),
+                                  "how": "h2d: 512 MiB pinned->device cudaMemcpyAsync per rank, all ranks at once, all bytes over the "
+                                         "slowest rank's time, best of 8 trials (h2d_calibrated), or the tmpfs zero-copy load's rate when "
+                                         "that was higher; page_cache_read: every rank's reader threads copy their shard out of the "
+                                         "file's mapping into cache-resident scratch (strom_debug_pagecache_read: no ring, no device), "
+                                         "all ranks at once, best of 3; pipeline_source (diagnosis): MEMCPY_SSD2GPU with the device "
+                                         "copy switched off"},
+            "engine": dict(abi.engine_state(local_rank), cpus_of_rank0=len(cpus_mine)),
         }
+        if c5 is not None:
+            result["c5_bit_exact"] = c5["bit_exact"]
+            result["c5"] = c5
         if tmpfs:
             result["e2e_tmpfs_zero_copy"] = tmpfs
         result.update(extras)
@@ -464,14 +541,16 @@ def run_product(args):
     if world == 1 and rank == 0 and not args.no_cpu:
         heapgen_file(path, SEED, PAGES_PER_GIB)
         try:
-            threads = os.cpu_count() or 1
+            threads = len(os.sched_getaffinity(0)) or 1
             one_gbps, one_ph, _ = cpu_path(path, 256 << 20, 1, 1, do_compare=True)
             cpu_path(path, GIB, threads, 1)
-            passes = 6
+            passes = 8
             all_gbps, all_ph, _ = cpu_path(path, GIB, threads, passes)
             result["cpu_baseline"] = {
                 "value": round(all_gbps, 3), "unit": "GB/s", "cores": threads, "kind": "port",
-                "sample": f"{passes} passes over the 1 GiB file (read + checksum/validate, no compare), warm page cache",
+                "sample": f"{passes} passes over the 1 GiB file (read + checksum/validate, no compare), warm page cache; "
+                          "threads and 32 MB buffers set up once outside the timed passes",
+                "phases_per_pass_s": {k: round(v, 4) for k, v in all_ph.items()},
                 "single_thread_GBps": round(one_gbps, 3),
                 "single_thread_phases_256MiB": {k: round(v, 4) for k, v in one_ph.items()}}
         finally:
@@ -491,6 +570,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--quick", action="store_true", help="skip the extra verify/load-only measurements")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-c5", action="store_true", help="skip the untimed mixed-validity (C5) exact-count leg")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

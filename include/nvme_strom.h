@@ -239,6 +239,13 @@ int nvme_strom_pin_file(int fdesc);
  * GPU's share of a file sharded over several processes needs */
 int nvme_strom_pin_file_range(int fdesc, uint64_t offset, uint64_t length);
 
+/* Forget the library's cached view of the file behind fdesc: its pages are unlocked and the
+ * mapping released as soon as the last transfer reading from it has finished.  (Views that were
+ * never page-locked are dropped on their own after NVME_STROM_MAP_IDLE_S seconds without use,
+ * default 30, so that a deleted file does not stay allocated behind the library's back.)
+ * Returns 0, or -1/errno when fdesc is not an open file. */
+int nvme_strom_unpin_file(int fdesc);
+
 /* The text the proc entry returns on read(2) (kmod/nvme_strom.c:2036-2061).
  * Copies at most len bytes, returns the number copied. */
 size_t nvme_strom_version(char *buf, size_t len);

@@ -40,6 +40,34 @@ int strom_file_extents_debug(int fd, uint64_t *extents, uint32_t max_extents);
  * the transfer roofline.  Returns the previous setting.  Never leave it on. */
 int strom_debug_skip_h2d(int on);
 
+/* Page-cache read rate of [offset, offset+length) of an open file, measured with n_threads readers
+ * (0: as many as an engine may use) that copy the engine's sub-pieces out of the file's mapping
+ * into a small private scratch each: no staging ring, no device.  The independent "source" term of
+ * the transfer roofline.  *seconds = wall time of the pass.  0, or -1 with errno (ENOTSUP: the
+ * file cannot be mapped / NVME_STROM_SRC=pread; EIO: a read faulted). */
+int strom_debug_pagecache_read(int fdesc, uint64_t offset, uint64_t length, int n_threads, double *seconds);
+
+/* Tuning tools only: tears the idle engines down and re-reads the NVME_STROM_* environment, so that
+ * one process can sweep staging geometries.  -1/EBUSY while a transfer is in flight.  Windows stay
+ * mapped; the next MEMCPY_* call builds new engines. */
+int strom_debug_reconfigure(void);
+
+/* What an engine decided for itself (reader self-adjustment, ring geometry). */
+typedef struct StromEngineState {
+	int32_t  allowed_cpus;       /* cores the engine counts on (affinity mask or NVME_STROM_CPUS)   */
+	uint32_t slot_bytes;
+	int32_t  slots;
+	int32_t  readers_max;
+	int32_t  adaptive;
+	int32_t  readers;            /* threads the engine of `device` has                              */
+	int32_t  readers_active;     /* how many of them take part at the moment                        */
+	uint64_t grown, shrunk;      /* adjustments so far                                              */
+	uint64_t slots_staged;       /* staged slots sent up                                            */
+	uint64_t slots_starved;      /* ... that found the link idle although more pieces were waiting  */
+} StromEngineState;
+/* -1/ENOENT when `device` has no engine yet (the configuration fields are filled in any case) */
+int strom_debug_engine_state(int device, StromEngineState *out);
+
 #ifdef __cplusplus
 }
 #endif

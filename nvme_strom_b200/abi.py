@@ -121,6 +121,36 @@ lib.nvme_strom_open.restype = C.c_int
 lib.nvme_strom_close.argtypes = [C.c_int]
 lib.nvme_strom_pin_file.argtypes = [C.c_int]
 lib.nvme_strom_pin_file_range.argtypes = [C.c_int, C.c_uint64, C.c_uint64]
+lib.nvme_strom_unpin_file.argtypes = [C.c_int]
+lib.strom_debug_pagecache_read.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
+
+
+class StromEngineState(C.Structure):
+    _fields_ = [("allowed_cpus", C.c_int32), ("slot_bytes", C.c_uint32), ("slots", C.c_int32),
+                ("readers_max", C.c_int32), ("adaptive", C.c_int32), ("readers", C.c_int32),
+                ("readers_active", C.c_int32), ("grown", C.c_uint64), ("shrunk", C.c_uint64),
+                ("slots_staged", C.c_uint64), ("slots_starved", C.c_uint64)]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
+lib.strom_debug_engine_state.argtypes = [C.c_int, C.POINTER(StromEngineState)]
+
+
+def engine_state(device):
+    """what the engine of `device` decided for itself (dict); fields about the engine are 0 when
+    there is none yet"""
+    st = StromEngineState()
+    lib.strom_debug_engine_state(device, C.byref(st))
+    return st.as_dict()
+
+
+def pagecache_read_GBps(fd, offset, length, n_threads=0):
+    """page-cache read rate of a file range (strom_debug.h), GB/s"""
+    secs = C.c_double()
+    check(lib.strom_debug_pagecache_read(fd, offset, length, n_threads, C.byref(secs)), "strom_debug_pagecache_read")
+    return length / secs.value / 1e9
 lib.nvme_strom_version.argtypes = [C.c_char_p, C.c_size_t]
 lib.nvme_strom_version.restype = C.c_size_t
 

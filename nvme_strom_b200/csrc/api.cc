@@ -200,7 +200,7 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 	const uint64_t req_bytes = (uint64_t)arg->nr_chunks * arg->chunk_sz;
 	const uint64_t first_fpos = arg->nr_chunks ? (uint64_t)(arg->relseg_sz ? arg->chunk_ids[0] % arg->relseg_sz
 																			 : arg->chunk_ids[0]) * arg->chunk_sz : 0;
-	in.piece_max = (source && source->range_locked(first_fpos, req_bytes)) ? (64u << 20)
+	in.piece_max = (source && source->range_locked(first_fpos, req_bytes)) ? engine_zero_copy_piece()
 																			: engine_piece_for(req_bytes);
 	Plan plan;
 	if ((rc = plan_chunks(in, &plan)) != 0)

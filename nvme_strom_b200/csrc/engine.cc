@@ -9,16 +9,22 @@
  * module, so each piece goes   file --copy--> pinned slot --H2D--> HBM   and
  * the pipeline's job is to keep both halves busy at once:
  *
- *   - one engine per (device, context): N reader threads, one ring of SLOTS
- *     pinned slots (4 x 4 MB), one CUDA stream, one event per slot;
+ *   - one engine per (device, context): reader threads, one ring of pinned
+ *     slots, one CUDA stream, one event per slot;
  *   - a piece is one slot.  Readers take 256 KB sub-pieces of the slot being
  *     filled; whoever finishes the last one queues the copy of the whole slot
  *     and everybody moves on to the next slot of the ring while it is in
  *     flight; a slot's event is waited for only when the ring comes round to
  *     it, or when there is nothing else to do;
- *   - the ring, not readers x slots, is what the CPU caches must hold, so the
- *     footprint stays at 16 MB per GPU whatever the reader count (see
- *     shared_worker and profiles/r01_slot_sweep.txt);
+ *   - the ring, not readers x slots, is what the CPU caches must hold, and it
+ *     is sized by the cores the process may run on (2 MB of L2 each): 4 x 4 MB
+ *     from 8 cores up, 4 x 2 MB on 4 (one rank of eight on a 32-core host);
+ *   - the number of readers that take part follows the copy stream: a slot
+ *     queued behind a copy that had already finished, with more pieces
+ *     waiting, means the source side starved the link, and another reader is
+ *     let in; a long run without a single such slot lets one go again.  The
+ *     rest stay parked and cost nothing (profiles/r02_*: past the link-bound
+ *     point extra readers only add lock and wake-up traffic);
  *   - page-locked sources (nvme_strom_pin_file) skip the staging: the copy
  *     engine reads the page cache itself and the slot lends only its event;
  *   - completion is a host-side refcount drop (task_put): MEMCPY_WAIT sleeps
@@ -28,16 +34,28 @@
  * SSD2RAM pieces have a host destination: read straight into the caller's
  * DMA buffer, no staging (kmod/nvme_strom.c:1693-1761).
  *
- * Environment: NVME_STROM_READERS (threads per engine, default min(16, 3/8 of the cpus):
- * the rest of the cores is left to the caller, the CUDA driver and SSD2RAM),
- * NVME_STROM_SLOT_KB (staging slot, default 4096), NVME_STROM_SLOTS (ring
- * length, default 4), NVME_STROM_SUB_KB (what one reader copies at a time,
- * default 256), NVME_STROM_SPIN_US (yield-spin before sleeping on a busy slot,
- * default 0: no measurable gain), NVME_STROM_HOST_READERS (SSD2RAM threads, default min(8, cpus)).
- * The first design (two slots and a stream per reader) is in the history; its numbers are
- * section A of profiles/r01_slot_sweep.txt.
+ * CPU placement (precedent: utils/ssd2ram_test.c:66-119 setup_cpu_affinity,
+ * pgsql/nvme_strom.c:300-378): the engine counts the cores the process is
+ * allowed on (sched_getaffinity), not the cores of the machine, and its
+ * threads inherit that mask -- a harness that runs one rank per GPU gives
+ * every rank its share of the cores (nvme_strom_b200/multigpu.py,
+ * strom_test -d) and each engine sizes itself to it.  NVME_STROM_CPUS=<list>
+ * pins an engine's readers to an explicit set instead.
+ *
+ * Environment: NVME_STROM_READERS (fixed reader count per engine; unset: self-
+ * adjusting between 2 and 3/4 of the allowed cores, at most 16),
+ * NVME_STROM_SLOT_KB (staging slot; unset: 4096, or 512 per allowed core below
+ * 8 cores), NVME_STROM_SLOTS (ring length, default 4), NVME_STROM_SUB_KB (what
+ * one reader copies at a time, default 256), NVME_STROM_SPIN_US (yield-spin
+ * before sleeping on a busy slot, default 0: no measurable gain),
+ * NVME_STROM_HOST_READERS (SSD2RAM threads, default min(8, cores)),
+ * NVME_STROM_COPY (memcpy | nta | ntstore).  All are read when the first engine
+ * is made (strom_debug_reconfigure() re-reads them: tuning tools only).
  */
 #include "strom_internal.h"
+#include "strom_debug.h"
+#include <csetjmp>
+#include <csignal>
 #include <cstring>
 #include <deque>
 #include <immintrin.h>
@@ -57,25 +75,113 @@ static std::atomic<int> g_skip_h2d{0};      /* strom_debug_skip_h2d(): calibrati
 static int env_int(const char *name, int dflt, int lo, int hi)
 {
 	const char *e = getenv(name);
-	int v = e ? atoi(e) : dflt;
+	int v = (e && *e) ? atoi(e) : dflt;
 	return v < lo ? lo : (v > hi ? hi : v);
 }
 
-uint32_t engine_piece_max()
+/* "0-3,8,10-11" -> cpu set; false when the text is not a list */
+static bool parse_cpu_list(const char *text, cpu_set_t *set)
 {
-	static uint32_t v = (uint32_t)env_int("NVME_STROM_SLOT_KB", 4096, 128, 65536) << 10;
-	return v;
+	CPU_ZERO(set);
+	int n = 0;
+	for (const char *p = text; *p;)
+	{
+		char *end = nullptr;
+		long a = strtol(p, &end, 10), b = a;
+		if (end == p || a < 0)
+			return false;
+		if (*end == '-')
+		{
+			const char *q = end + 1;
+			b = strtol(q, &end, 10);
+			if (end == q || b < a)
+				return false;
+		}
+		for (long c = a; c <= b && c < CPU_SETSIZE; c++, n++)
+			CPU_SET((int)c, set);
+		p = (*end == ',') ? end + 1 : end;
+		if (*end && *end != ',')
+			return false;
+	}
+	return n > 0;
 }
 
-static int gpu_reader_count()
+/*
+ * What the engines are built from.  Read once, when the first engine is made.
+ */
+struct EngineConfig {
+	int      ncpu = 1;               /* cores this process may run on (or NVME_STROM_CPUS)       */
+	bool     pin = false;            /* NVME_STROM_CPUS given: readers are bound to `cpus`        */
+	cpu_set_t cpus;
+	uint32_t slot_bytes = 4u << 20;
+	uint32_t sub_bytes = 256u << 10;
+	int      slots = 4;
+	int      readers_start = 2, readers_max = 2;
+	bool     adaptive = true;
+	int      host_readers = 1;
+	int      copy_mode = 0;          /* 0 memcpy, 1 nta, 2 ntstore                              */
+	bool     write_combined = false;
+	int      spin_us = 0;
+	uint32_t zero_copy_piece = 64u << 20;   /* page-locked sources: one cudaMemcpyAsync per this much */
+};
+
+static EngineConfig load_config()
 {
-	int ncpu = (int)std::thread::hardware_concurrency();
-	if (ncpu < 1) ncpu = 8;
-	/* 3/8 of the cores: a single GPU is link-bound from 6 readers on, and the rest is needed by the
-	 * caller, the driver's threads and the SSD2RAM engine (with 8 + 8 readers on 16 cores the
-	 * two-way compare of bench.py lost a fifth of its rate to descheduled readers) */
-	return env_int("NVME_STROM_READERS", std::max(2, std::min(ncpu * 3 / 8, 16)), 1, 256);
+	EngineConfig c;
+	CPU_ZERO(&c.cpus);
+	const char *list = getenv("NVME_STROM_CPUS");
+	if (list && *list && parse_cpu_list(list, &c.cpus))
+		c.pin = true;
+	else if (sched_getaffinity(0, sizeof(c.cpus), &c.cpus) != 0)
+		CPU_ZERO(&c.cpus);
+	c.ncpu = CPU_COUNT(&c.cpus);
+	if (c.ncpu < 1)
+	{
+		c.ncpu = (int)std::thread::hardware_concurrency();
+		if (c.ncpu < 1) c.ncpu = 8;
+		c.pin = false;
+	}
+	/* ring: 4 slots; what the readers' cores can keep in their caches (2 MB of L2 each) */
+	const int slot_kb_dflt = c.ncpu >= 8 ? 4096 : std::max(1024, c.ncpu * 512);
+	c.slot_bytes = (uint32_t)env_int("NVME_STROM_SLOT_KB", slot_kb_dflt, 128, 65536) << 10;
+	c.slots = env_int("NVME_STROM_SLOTS", 4, 2, 64);
+	c.sub_bytes = (uint32_t)env_int("NVME_STROM_SUB_KB", 256, 64, 65536) << 10;
+	/* readers: a lone GPU is link-bound from about 6 on; the rest of the cores is needed by the
+	 * caller, the driver's threads and the SSD2RAM engine.  Up to 4 cores every core reads (the
+	 * caller sleeps in MEMCPY_WAIT meanwhile). */
+	c.readers_max = c.ncpu <= 4 ? std::max(2, c.ncpu) : std::min(16, c.ncpu * 3 / 4);
+	c.readers_start = std::min(c.readers_max, std::max(2, std::min(6, c.ncpu * 3 / 8)));
+	const char *fixed = getenv("NVME_STROM_READERS");
+	if (fixed && *fixed)
+	{
+		c.readers_start = c.readers_max = env_int("NVME_STROM_READERS", 2, 1, 256);
+		c.adaptive = false;
+	}
+	if (env_int("NVME_STROM_ADAPTIVE", 1, 0, 1) == 0)
+		c.adaptive = false;
+	c.host_readers = env_int("NVME_STROM_HOST_READERS", std::min(c.ncpu, 8), 1, 256);
+	const char *m = getenv("NVME_STROM_COPY");
+	if (m && __builtin_cpu_supports("avx2"))
+		c.copy_mode = !strcmp(m, "nta") ? 1 : (!strcmp(m, "ntstore") ? 2 : 0);
+	c.write_combined = env_int("NVME_STROM_WC", 0, 0, 1) != 0;
+	c.spin_us = env_int("NVME_STROM_SPIN_US", 0, 0, 100000);
+	c.zero_copy_piece = (uint32_t)env_int("NVME_STROM_ZC_PIECE_MB", 64, 1, 64) << 20;
+	return c;
 }
+
+static std::mutex g_config_lock;
+static std::shared_ptr<const EngineConfig> g_config;
+
+static std::shared_ptr<const EngineConfig> config()
+{
+	std::lock_guard<std::mutex> g(g_config_lock);
+	if (!g_config)
+		g_config = std::make_shared<const EngineConfig>(load_config());
+	return g_config;
+}
+
+uint32_t engine_piece_max() { return config()->slot_bytes; }
+uint32_t engine_zero_copy_piece() { return config()->zero_copy_piece; }
 
 /* Every reader works on the same slot, so a piece is simply a slot (or the whole request when
  * that is smaller); small requests need no special cut to keep the readers busy. */
@@ -111,7 +217,7 @@ static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
 
 /*
  * NVME_STROM_COPY selects how a sub-piece leaves the page cache (experiments for hosts whose caches
- * are the bottleneck, profiles/r01_slot_sweep.txt; default "memcpy"):
+ * are the bottleneck; default "memcpy", which profiles/r02_copy_modes.txt shows is the right one):
  *   nta      source lines are prefetched non-temporally ahead of the loads, so that page-cache
  *            bytes, which are read exactly once, do not push the staging ring out of the caches;
  *   ntstore  as nta, and the staging slot is written with streaming stores (the ring then lives in
@@ -119,17 +225,6 @@ static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
  * Both need AVX2 and 32-byte alignment (sub-pieces are 4 KB aligned on both sides); anything else
  * falls back to memcpy.
  */
-static int copy_mode()
-{
-	static const int v = [] {
-		const char *e = getenv("NVME_STROM_COPY");
-		if (!e || !__builtin_cpu_supports("avx2"))
-			return 0;
-		return !strcmp(e, "nta") ? 1 : (!strcmp(e, "ntstore") ? 2 : 0);
-	}();
-	return v;
-}
-
 __attribute__((target("avx2"))) static void copy_lines_avx2(char *dst, const char *src, uint64_t n, bool stream_stores)
 {
 	constexpr uint64_t kAhead = 1024;                     /* bytes of source prefetched ahead */
@@ -157,17 +252,73 @@ __attribute__((target("avx2"))) static void copy_lines_avx2(char *dst, const cha
 		memcpy(dst + i, src + i, n - i);
 }
 
-/* piece [off, off+len) out of the mapped file; zeros past EOF like read_fully */
-static void copy_from_map(const SourceMap &m, char *dst, uint32_t len, uint64_t off)
+/*
+ * Reading a file through a mapping turns an I/O error -- a media error under a page that has to be
+ * read in, or a truncation that lands after the size was taken -- into SIGBUS in the reading thread,
+ * where pread() would have returned EIO.  The module reports such failures as the task's status
+ * through MEMCPY_WAIT (kmod/nvme_strom.c:993-1039, :1163-1168); to keep that, every copy out of a
+ * source mapping runs under a per-thread recovery point: the handler jumps back when the faulting
+ * thread is inside such a copy, and hands the signal on to whoever owned it before in every other
+ * case.  (A host program that installs its own SIGBUS handler AFTER the first load replaces this
+ * one; NVME_STROM_SRC=pread avoids the mapping altogether.)
+ */
+static thread_local sigjmp_buf *t_bus_recover = nullptr;
+static struct sigaction g_bus_previous;
+
+static void bus_handler(int sig, siginfo_t *info, void *uc)
 {
-	uint64_t n = off < m.size ? std::min<uint64_t>(len, m.size - off) : 0;
-	const int mode = copy_mode();
+	if (t_bus_recover)
+		siglongjmp(*t_bus_recover, 1);
+	if (g_bus_previous.sa_flags & SA_SIGINFO)
+	{
+		if (g_bus_previous.sa_sigaction)
+			g_bus_previous.sa_sigaction(sig, info, uc);
+		return;
+	}
+	if (g_bus_previous.sa_handler == SIG_IGN)
+		return;
+	if (g_bus_previous.sa_handler != SIG_DFL)
+	{
+		g_bus_previous.sa_handler(sig);
+		return;
+	}
+	signal(SIGBUS, SIG_DFL);                              /* not ours: die the way the process would have */
+	raise(SIGBUS);
+}
+
+static void install_bus_guard()
+{
+	static std::once_flag once;
+	std::call_once(once, [] {
+		struct sigaction sa;
+		memset(&sa, 0, sizeof(sa));
+		sa.sa_sigaction = bus_handler;
+		sa.sa_flags = SA_SIGINFO | SA_NODEFER;
+		sigemptyset(&sa.sa_mask);
+		sigaction(SIGBUS, &sa, &g_bus_previous);
+	});
+}
+
+/* piece [off, off+len) out of the mapped file; zeros past EOF like read_fully; 0 or -EIO */
+static int copy_from_map(const SourceMap &m, char *dst, uint32_t len, uint64_t off, int mode)
+{
+	const uint64_t n = off < m.size ? std::min<uint64_t>(len, m.size - off) : 0;
+	sigjmp_buf recover;
+	if (sigsetjmp(recover, 1) != 0)
+	{
+		t_bus_recover = nullptr;
+		logf(1, "source mapping: SIGBUS while reading [%llu, +%u): reported as EIO", (unsigned long long)off, len);
+		return -EIO;
+	}
+	t_bus_recover = &recover;
 	if (n && mode && (((uintptr_t)dst | (uintptr_t)(m.base + off)) & 31) == 0)
 		copy_lines_avx2(dst, m.base + off, n, mode == 2);
 	else if (n)
 		memcpy(dst, m.base + off, n);
+	t_bus_recover = nullptr;
 	if (n < len)
 		memset(dst + n, 0, len - n);
+	return 0;
 }
 
 /* NVME_STROM_FAULT_EVERY=N: every Nth piece fails with EIO, as a read error on the
@@ -182,15 +333,12 @@ static int injected_fault()
 	return (counter.fetch_add(1) + 1) % (uint64_t)every == 0 ? -EIO : 0;
 }
 
-static int fetch_piece(const Job &j, char *dst)
+static int fetch_piece(const Job &j, char *dst, int copy_mode)
 {
 	if (int rc = injected_fault())
 		return rc;
 	if (j.src && !j.direct)
-	{
-		copy_from_map(*j.src, dst, j.length, j.file_off);
-		return 0;
-	}
+		return copy_from_map(*j.src, dst, j.length, j.file_off, copy_mode);
 	return read_fully(j.fd, dst, j.length, j.file_off);
 }
 
@@ -281,6 +429,16 @@ static void pin_thread_main()
 	}
 }
 
+bool SourceMap::has_locked_regions() const
+{
+	if (!region_state)
+		return false;
+	for (uint64_t r = 0; r * kRegion < size; r++)
+		if (region_state[r].load(std::memory_order_acquire) == 1 || region_state[r].load() == 3)
+			return true;
+	return false;
+}
+
 bool SourceMap::range_locked(uint64_t off, uint64_t len) const
 {
 	if (!pinnable || !region_state || len == 0 || off + len > size)
@@ -339,17 +497,40 @@ std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st)
 	static std::vector<std::shared_ptr<SourceMap>> &cache = *new std::vector<std::shared_ptr<SourceMap>>();
 	if (!enabled || st.st_size <= 0)
 		return nullptr;
+	install_bus_guard();
+	struct timespec now_ts;
+	clock_gettime(CLOCK_MONOTONIC, &now_ts);
+	const int64_t now = (int64_t)now_ts.tv_sec;
 	std::lock_guard<std::mutex> g(lock);
+	/* A cached mapping keeps a deleted file's blocks allocated.  Views nobody has asked for in a
+	 * while are dropped (tasks in flight hold their own reference, so a view goes away only when
+	 * the last of them is done); page-locked ones stay until nvme_strom_unpin_file(): locking is
+	 * expensive and was asked for.  (fd < 0: the explicit drop of one file.) */
+	static const int64_t idle_s = env_int("NVME_STROM_MAP_IDLE_S", 30, 0, 1 << 30);
+	for (size_t i = 0; i < cache.size();)
+	{
+		SourceMap &m = *cache[i];
+		const bool is_this = m.dev == (uint64_t)st.st_dev && m.ino == (uint64_t)st.st_ino;
+		if ((fd < 0 && is_this) || (!is_this && !m.has_locked_regions() && now - m.last_used_s > idle_s))
+			cache.erase(cache.begin() + (long)i);
+		else
+			i++;
+	}
+	if (fd < 0)
+		return nullptr;
 	for (size_t i = 0; i < cache.size(); i++)
 	{
-		const SourceMap &m = *cache[i];
+		SourceMap &m = *cache[i];
 		if (m.dev == (uint64_t)st.st_dev && m.ino == (uint64_t)st.st_ino)
 		{
 			/* a MAP_SHARED view always shows the file's current bytes; only a size change makes
 			 * the mapping stale.  (mtime is useless here: page-locking a writable shared mapping
 			 * of a tmpfs file touches it.) */
 			if (m.size == (uint64_t)st.st_size)
+			{
+				m.last_used_s = now;
 				return cache[i];
+			}
 			cache.erase(cache.begin() + (long)i);
 			break;
 		}
@@ -391,6 +572,7 @@ std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st)
 	m->mtime_s = st.st_mtim.tv_sec;
 	m->mtime_ns = st.st_mtim.tv_nsec;
 	m->base = static_cast<char *>(p);
+	m->last_used_s = now;
 	if (cache.size() >= 16)
 		cache.erase(cache.begin());
 	cache.push_back(m);
@@ -399,12 +581,11 @@ std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st)
 
 class Engine {
 public:
-	Engine(int device, void *ctx, bool host_only)
-		: device_(device), ctx_(ctx), host_only_(host_only)
+	Engine(int device, void *ctx, bool host_only, std::shared_ptr<const EngineConfig> cfg)
+		: cfg_(std::move(cfg)), device_(device), ctx_(ctx), host_only_(host_only)
 	{
-		int ncpu = (int)std::thread::hardware_concurrency();
-		if (ncpu < 1) ncpu = 8;
-		int n = host_only ? env_int("NVME_STROM_HOST_READERS", std::min(ncpu, 8), 1, 256) : gpu_reader_count();
+		const int n = host_only ? cfg_->host_readers : cfg_->readers_max;
+		active_ = host_only ? n : cfg_->readers_start;
 		for (int i = 0; i < n; i++)
 			threads_.emplace_back([this, i] { worker(i); });
 		/* Return only when every worker has its stream, events and pinned slots: page-locked
@@ -413,7 +594,7 @@ public:
 		std::unique_lock<std::mutex> g(lock_);
 		ready_cv_.wait(g, [&] { return ready_ == n; });
 	}
-	/* engines live until process exit; threads are detached at teardown */
+	/* engines live until process exit (or strom_debug_reconfigure) */
 	~Engine()
 	{
 		{
@@ -421,8 +602,16 @@ public:
 			stop_ = true;
 		}
 		cv_.notify_all();
+		park_cv_.notify_all();
 		for (auto &t : threads_)
 			t.join();
+		for (Stage &st : stages_)
+		{
+			if (st.ev) (void)cudaEventDestroy(st.ev);
+			if (st.buf) (void)cudaFreeHost(st.buf);
+		}
+		if (stream_) (void)cudaStreamDestroy(stream_);
+		(void)cudaGetLastError();
 	}
 	void submit(const std::vector<Job> &jobs)
 	{
@@ -435,6 +624,26 @@ public:
 			cv_.notify_all();                     /* GPU engine: every reader helps with one piece */
 		else
 			cv_.notify_one();
+	}
+	bool idle()
+	{
+		std::lock_guard<std::mutex> g(lock_);
+		if (!queue_.empty() || open_ >= 0)
+			return false;
+		for (const Stage &st : stages_)
+			if (st.state != kFree)
+				return false;
+		return true;
+	}
+	void state(int *active, int *readers, uint64_t *grown, uint64_t *shrunk, uint64_t *starved, uint64_t *issued)
+	{
+		std::lock_guard<std::mutex> g(lock_);
+		*active = active_;
+		*readers = (int)threads_.size();
+		*grown = n_grown_;
+		*shrunk = n_shrunk_;
+		*starved = n_starved_;
+		*issued = n_issued_;
 	}
 
 private:
@@ -459,7 +668,8 @@ private:
 
 	void worker(int index)
 	{
-		(void)index;
+		if (cfg_->pin)
+			(void)sched_setaffinity(0, sizeof(cfg_->cpus), &cfg_->cpus);
 		if (host_only_)
 		{
 			mark_ready();
@@ -468,7 +678,7 @@ private:
 			{
 				const uint64_t t0 = rdtsc_now();
 				stats_dma_started();
-				int rc = fetch_piece(j, j.dst);
+				int rc = fetch_piece(j, j.dst, 0);
 				stats_dma_finished(t0);
 				task_put(j.task, rc);
 			}
@@ -483,8 +693,8 @@ private:
 	}
 
 	/* ---- shared staging ring ------------------------------------------------------------
-	 * The ring is what the CPU caches have to hold: slots x slot size per GPU (16 MB by default)
-	 * however many readers there are, so the staged bytes are still in cache when the slot is
+	 * The ring is what the CPU caches have to hold: slots x slot size per GPU however many
+	 * readers there are, so the staged bytes are still in cache when the slot is
 	 * written again, and eight engines on one host do not evict each other (profiles/
 	 * r01_slot_sweep.txt: with private slots the footprint was readers x 2 x slot, and the box's
 	 * aggregate rate fell as it grew).  A piece is one slot; readers take 256 KB sub-pieces of the
@@ -503,6 +713,7 @@ private:
 		uint32_t next_off = 0;            /* next sub-piece to hand out                    */
 		uint32_t unfilled = 0;            /* sub-pieces handed out or still to hand out    */
 		long status = 0;                  /* first error among the fillers                 */
+		bool backlog = false;             /* more pieces were waiting when this one was taken */
 	};
 
 	void retire_stage(Stage &st)
@@ -518,11 +729,15 @@ private:
 		st.task = nullptr;
 	}
 
-	/* send [buf, buf+len) or, for a page-locked source, the page cache itself; 0 or -EIO */
-	int issue_copy(Stage &st, bool from_source)
+	/* send [buf, buf+len) or, for a page-locked source, the page cache itself; 0 or -EIO.
+	 * *link_idle: the copy queued before this one had already finished, i.e. the link was waiting
+	 * for the readers. */
+	int issue_copy(Stage &st, bool from_source, bool *link_idle)
 	{
 		const Job &j = st.piece;
 		std::lock_guard<std::mutex> g(issue_lock_);       /* copy + its event, not interleaved */
+		*link_idle = last_event_ != nullptr && cudaEventQuery(last_event_) == cudaSuccess;
+		(void)cudaGetLastError();                         /* cudaErrorNotReady is not an error */
 		cudaError_t cr = cudaSuccess;
 		if (from_source)
 		{
@@ -546,7 +761,64 @@ private:
 			(void)cudaGetLastError();
 			return -EIO;
 		}
+		last_event_ = st.ev;
 		return 0;
+	}
+
+	/*
+	 * How many readers take part (lock held).  Evidence is gathered over windows of 16 staged
+	 * slots: a slot counts as starved when it was queued behind a finished copy although more
+	 * pieces were waiting -- the readers, not the link, set the pace.  A quarter of a window
+	 * starved lets one more reader in; eight windows in a row without a single starved slot let
+	 * one go.  When letting one go is answered by starvation at once, the count goes back up and
+	 * stays put for a while that doubles every time (the link-bound point has been found; there
+	 * is no reason to keep probing it).
+	 */
+	void account_slot(bool starved)
+	{
+		n_issued_++;
+		if (starved)
+			n_starved_++;
+		if (!cfg_->adaptive)
+			return;
+		win_issued_++;
+		if (starved)
+			win_starved_++;
+		if (win_issued_ < 16)
+			return;
+		const int max = (int)threads_.size();
+		if (win_starved_ * 4 >= win_issued_)
+		{
+			if (active_ < max)
+			{
+				active_++;
+				n_grown_++;
+				park_cv_.notify_all();
+			}
+			if (since_shrink_ <= 2)                   /* that reader was needed */
+			{
+				hold_ = hold_next_;
+				hold_next_ = std::min<uint32_t>(hold_next_ * 2, 4096);
+			}
+			calm_ = 0;
+		}
+		else if (win_starved_ == 0)
+		{
+			if (hold_ > 0)
+				hold_--;
+			else if (++calm_ >= 8 && active_ > 2)
+			{
+				active_--;
+				n_shrunk_++;
+				calm_ = 0;
+				since_shrink_ = 0;
+			}
+		}
+		else
+			calm_ = 0;
+		if (since_shrink_ < 1000)
+			since_shrink_++;
+		win_issued_ = win_starved_ = 0;
 	}
 
 	/* A reader that has to wait for a slot waits for a copy to finish, some tens of
@@ -554,7 +826,7 @@ private:
 	 * the change counter for a while before going to sleep.  Call with the lock held. */
 	void wait_for_change(std::unique_lock<std::mutex> &g)
 	{
-		static const uint64_t spin_cycles = (uint64_t)env_int("NVME_STROM_SPIN_US", 0, 0, 100000) * 2000;
+		const uint64_t spin_cycles = (uint64_t)cfg_->spin_us * 2000;
 		const uint64_t seen = changes_.load(std::memory_order_relaxed);
 		if (spin_cycles)
 		{
@@ -575,12 +847,13 @@ private:
 
 	void shared_worker(int index, bool bound)
 	{
-		const uint32_t slot_sz = engine_piece_max();
-		const uint32_t sub_sz = (uint32_t)env_int("NVME_STROM_SUB_KB", 256, 64, 65536) << 10;
+		const uint32_t slot_sz = cfg_->slot_bytes;
+		const uint32_t sub_sz = cfg_->sub_bytes;
+		const int copy_mode = cfg_->copy_mode;
 		if (index == 0)
 		{
-			const int n = env_int("NVME_STROM_SLOTS", 4, 2, 64);
-			const unsigned wc_flag = env_int("NVME_STROM_WC", 0, 0, 1) ? cudaHostAllocWriteCombined : 0;
+			const int n = cfg_->slots;
+			const unsigned wc_flag = cfg_->write_combined ? cudaHostAllocWriteCombined : 0;
 			std::vector<Stage> ring((size_t)n);
 			bool ok = bound && cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking) == cudaSuccess;
 			for (int i = 0; ok && i < n; i++)
@@ -600,6 +873,13 @@ private:
 		std::unique_lock<std::mutex> g(lock_);
 		for (;;)
 		{
+			/* 0. not taking part for now: readers beyond the active count wait here, off the
+			 * condition variable that every slot change signals */
+			if (index >= active_ && !stop_)
+			{
+				park_cv_.wait(g);
+				continue;
+			}
 			/* 1. a sub-piece of the slot being filled */
 			if (open_ >= 0)
 			{
@@ -618,7 +898,7 @@ private:
 					Job part = o.piece;
 					part.file_off += off;
 					part.length = len;
-					const long rc = fetch_piece(part, o.buf + off);
+					const long rc = fetch_piece(part, o.buf + off, copy_mode);
 					g.lock();
 					if (rc != 0 && o.status == 0)
 						o.status = rc;
@@ -629,11 +909,11 @@ private:
 					g.unlock();
 					const uint64_t t0 = rdtsc_now();
 					long done_rc = status;
-					bool in_flight = false;
+					bool in_flight = false, link_idle = false;
 					if (status == 0 && !g_skip_h2d.load(std::memory_order_relaxed))
 					{
 						stats_dma_started();
-						done_rc = issue_copy(o, false);
+						done_rc = issue_copy(o, false, &link_idle);
 						in_flight = done_rc == 0;
 						if (!in_flight)
 							stats_dma_finished(t0);
@@ -651,6 +931,7 @@ private:
 					{
 						o.task = o.piece.task;
 						o.tsc = t0;
+						account_slot(link_idle && o.backlog);
 					}
 					o.state = in_flight ? kInFlight : kFree;
 					announce_change();
@@ -681,6 +962,7 @@ private:
 				ring_next_ = (ring_next_ + 1) % (int)stages_.size();
 				Job j = queue_.front();
 				queue_.pop_front();
+				n.backlog = !queue_.empty();
 				n.state = kPreparing;
 				open_ = idx;
 				g.unlock();
@@ -694,11 +976,12 @@ private:
 					 * slot lends only its event */
 					const uint64_t t0 = rdtsc_now();
 					long rc = injected_fault();
+					bool link_idle = false;
 					n.piece = j;
 					if (rc == 0)
 					{
 						stats_dma_started();
-						rc = issue_copy(n, true);
+						rc = issue_copy(n, true, &link_idle);
 						if (rc != 0)
 							stats_dma_finished(t0);
 					}
@@ -733,7 +1016,10 @@ private:
 				}
 				g.lock();
 				if (split)
+				{
 					queue_.push_front(rest);
+					n.backlog = true;
+				}
 				n.piece = j;
 				n.next_off = 0;
 				n.unfilled = (j.length + sub_sz - 1) / sub_sz;
@@ -767,6 +1053,7 @@ private:
 		}
 	}
 
+	std::shared_ptr<const EngineConfig> cfg_;
 	int device_;
 	void *ctx_;
 	bool host_only_;
@@ -776,9 +1063,14 @@ private:
 	int open_ = -1;                       /* slot whose sub-pieces are handed out  */
 	cudaStream_t stream_ = nullptr;       /* the engine's one copy stream          */
 	std::mutex issue_lock_;
+	cudaEvent_t last_event_ = nullptr;    /* of the copy queued last (issue_lock_) */
 	std::atomic<uint64_t> changes_{0};    /* bumped on every slot state change     */
 	std::mutex lock_;
 	std::condition_variable cv_;
+	std::condition_variable park_cv_;     /* readers beyond active_ wait here      */
+	int active_ = 1;                      /* readers taking part                   */
+	uint32_t win_issued_ = 0, win_starved_ = 0, calm_ = 0, hold_ = 0, hold_next_ = 16, since_shrink_ = 1000;
+	uint64_t n_grown_ = 0, n_shrunk_ = 0, n_starved_ = 0, n_issued_ = 0;
 	std::deque<Job> queue_;
 	std::condition_variable ready_cv_;
 	int ready_ = 0;
@@ -797,7 +1089,7 @@ Engine *engine_for_window(const GpuWindow &w)
 	auto it = g_engines.find(key);
 	if (it != g_engines.end())
 		return it->second;
-	Engine *e = new Engine(w.device, w.ctx, false);
+	Engine *e = new Engine(w.device, w.ctx, false, config());
 	g_engines[key] = e;
 	return e;
 }
@@ -806,16 +1098,124 @@ Engine *engine_for_host()
 {
 	std::lock_guard<std::mutex> g(g_engine_lock);
 	if (!g_host_engine)
-		g_host_engine = new Engine(-1, nullptr, true);
+		g_host_engine = new Engine(-1, nullptr, true, config());
 	return g_host_engine;
 }
 
 void engine_submit(Engine *e, const std::vector<Job> &jobs) { e->submit(jobs); }
 
+/*
+ * Page-cache read rate, measured without the ring and without the device: n_threads readers share
+ * out [offset, offset+length) of the mapped file in the engine's sub-piece size and copy every
+ * sub-piece into a scratch of that size of their own, which stays in the core's cache -- what
+ * reaches DRAM is the read of the page cache and nothing else.  This is the "source" term of the
+ * transfer roofline (north_star: the slower of page-cache read bandwidth and PCIe H2D); it does
+ * not move with the staging geometry.
+ */
+static int pagecache_read_rate(int fd, uint64_t offset, uint64_t length, int n_threads, double *seconds)
+{
+	struct stat st;
+	if (fstat(fd, &st) != 0)
+		return -errno;
+	std::shared_ptr<SourceMap> m = source_map_get(fd, st);
+	if (!m)
+		return -ENOTSUP;
+	if (offset >= m->size)
+		return -ERANGE;
+	length = std::min<uint64_t>(length, m->size - offset);
+	std::shared_ptr<const EngineConfig> cfg = config();
+	if (n_threads <= 0)
+		n_threads = cfg->readers_max;
+	const uint32_t sub = cfg->sub_bytes;
+	std::atomic<uint64_t> cursor{0};
+	std::atomic<int> failed{0}, ready{0};
+	std::atomic<bool> go{false};
+	std::vector<std::thread> threads;
+	for (int t = 0; t < n_threads; t++)
+		threads.emplace_back([&] {
+			if (cfg->pin)
+				(void)sched_setaffinity(0, sizeof(cfg->cpus), &cfg->cpus);
+			void *scratch = nullptr;
+			if (posix_memalign(&scratch, 4096, sub) != 0) { failed++; ready++; return; }
+			memset(scratch, 0, sub);
+			ready++;
+			while (!go.load(std::memory_order_acquire))
+				sched_yield();
+			for (;;)
+			{
+				const uint64_t at = cursor.fetch_add(sub);
+				if (at >= length)
+					break;
+				const uint32_t n = (uint32_t)std::min<uint64_t>(sub, length - at);
+				if (copy_from_map(*m, (char *)scratch, n, offset + at, 0) != 0)
+					failed++;
+			}
+			free(scratch);
+		});
+	while (ready.load() < n_threads)
+		sched_yield();
+	struct timespec t0, t1;
+	clock_gettime(CLOCK_MONOTONIC, &t0);
+	go.store(true, std::memory_order_release);
+	for (auto &t : threads)
+		t.join();
+	clock_gettime(CLOCK_MONOTONIC, &t1);
+	*seconds = (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+	return failed.load() ? -EIO : 0;
+}
+
 } /* namespace strom */
 
-#include "strom_debug.h"
 extern "C" int strom_debug_skip_h2d(int on) { return strom::g_skip_h2d.exchange(on ? 1 : 0); }
+
+extern "C" int strom_debug_pagecache_read(int fdesc, uint64_t offset, uint64_t length, int n_threads, double *seconds)
+{
+	if (!seconds) { errno = EINVAL; return -1; }
+	int rc = strom::pagecache_read_rate(fdesc, offset, length, n_threads, seconds);
+	if (rc != 0) { errno = -rc; return -1; }
+	return 0;
+}
+
+extern "C" int strom_debug_reconfigure(void)
+{
+	using namespace strom;
+	std::lock_guard<std::mutex> g(g_engine_lock);
+	for (auto &kv : g_engines)
+		if (!kv.second->idle()) { errno = EBUSY; return -1; }
+	for (auto &kv : g_engines)
+		delete kv.second;
+	g_engines.clear();
+	delete g_host_engine;
+	g_host_engine = nullptr;
+	std::lock_guard<std::mutex> c(g_config_lock);
+	g_config = std::make_shared<const EngineConfig>(load_config());
+	return 0;
+}
+
+extern "C" int strom_debug_engine_state(int device, StromEngineState *out)
+{
+	using namespace strom;
+	if (!out) { errno = EINVAL; return -1; }
+	memset(out, 0, sizeof(*out));
+	std::shared_ptr<const EngineConfig> c = config();
+	out->allowed_cpus = c->ncpu;
+	out->slot_bytes = c->slot_bytes;
+	out->slots = c->slots;
+	out->readers_max = c->readers_max;
+	out->adaptive = c->adaptive;
+	std::lock_guard<std::mutex> g(g_engine_lock);
+	for (auto &kv : g_engines)
+		if (kv.first.first == device)
+		{
+			int active = 0, readers = 0;
+			kv.second->state(&active, &readers, &out->grown, &out->shrunk, &out->slots_starved, &out->slots_staged);
+			out->readers_active = active;
+			out->readers = readers;
+			return 0;
+		}
+	errno = ENOENT;
+	return -1;
+}
 
 extern "C" int nvme_strom_pin_file_range(int fdesc, uint64_t offset, uint64_t length)
 {
@@ -848,3 +1248,12 @@ extern "C" int nvme_strom_pin_file_range(int fdesc, uint64_t offset, uint64_t le
 }
 
 extern "C" int nvme_strom_pin_file(int fdesc) { return nvme_strom_pin_file_range(fdesc, 0, ~0ull); }
+
+extern "C" int nvme_strom_unpin_file(int fdesc)
+{
+	struct stat st;
+	if (fstat(fdesc, &st) != 0)
+		return -1;
+	(void)strom::source_map_get(-1, st);         /* drops the cached view; unlocked when its last task ends */
+	return 0;
+}

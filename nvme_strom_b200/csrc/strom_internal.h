@@ -80,6 +80,8 @@ struct SourceMap {
 	std::unique_ptr<std::atomic<int>[]> region_state;      /* 0 untouched, 1 locked, 2 refused, 3 in progress */
 	bool region_ready(uint64_t off, uint64_t len, const std::shared_ptr<SourceMap> &self, int device);
 	bool range_locked(uint64_t off, uint64_t len) const;    /* no side effects */
+	bool has_locked_regions() const;
+	int64_t last_used_s = 0;                                /* CLOCK_MONOTONIC seconds, cache lock held */
 	~SourceMap();
 };
 std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st);   /* null: use pread */
@@ -151,6 +153,7 @@ Engine *engine_for_host();
 void engine_submit(Engine *e, const std::vector<Job> &jobs);
 uint32_t engine_piece_max();                              /* staging slot size   */
 uint32_t engine_piece_for(uint64_t request_bytes);        /* piece size for one request */
+uint32_t engine_zero_copy_piece();                        /* piece size when the source is page-locked */
 
 /* ---- statistics (kmod/nvme_strom.c:64-86) --------------------------------------- */
 struct Stats {

@@ -619,11 +619,12 @@ int ora_plan_chunks(int to_gpu, uint32_t nr_chunks, uint32_t chunk_sz,
 typedef struct cpu_job {
 	int fd;
 	uint64_t segment_sz, n_segments;
-	int do_scan, do_compare;
+	int do_scan, do_compare, passes, n_threads;
 	uint64_t cursor;                 /* shared, __sync_fetch_and_add like ssd2ram_test.c:180 */
 	pthread_mutex_t lock;
-	ora_totals totals;
-	double t_read, t_scan, t_cmp;
+	pthread_barrier_t gate;          /* workers + the timing thread */
+	ora_totals totals;               /* of the last pass */
+	double t_read, t_scan, t_cmp;    /* summed over workers and passes */
 	int err;
 } cpu_job;
 
@@ -652,67 +653,90 @@ static int pread_full(int fd, uint8_t *buf, uint64_t len, uint64_t off)
 	return 0;
 }
 
+/*
+ * One worker.  Its two segment buffers are allocated and touched BEFORE the first gate, i.e.
+ * outside the timed region (the reference allocates its buffers once, at start-up:
+ * utils/nvme_test.c:276-323), and live across all passes.
+ */
 static void *cpu_worker(void *arg)
 {
 	cpu_job *job = arg;
 	uint8_t *a = NULL, *b = NULL;
-	ora_totals loc;
 	double t_read = 0, t_scan = 0, t_cmp = 0, t0;
-	uint64_t bad_first = ~(uint64_t)0;
 	int rc = 0;
 
-	memset(&loc, 0, sizeof(loc));
 	if (posix_memalign((void **)&a, 4096, job->segment_sz) ||
-		posix_memalign((void **)&b, 4096, job->segment_sz))
+		(job->do_compare && posix_memalign((void **)&b, 4096, job->segment_sz)))
 		rc = -ENOMEM;
-	while (rc == 0)
+	if (rc == 0)
 	{
-		uint64_t seg = __sync_fetch_and_add(&job->cursor, 1);
-		uint64_t fpos = seg * job->segment_sz;
-		uint64_t n_pages = job->segment_sz / ORA_BLCKSZ;
+		memset(a, 0, job->segment_sz);
+		if (b)
+			memset(b, 0, job->segment_sz);
+	}
+	for (int pass = 0; pass < job->passes; pass++)
+	{
+		ora_totals loc;
+		uint64_t bad_first = ~(uint64_t)0;
 
-		if (seg >= job->n_segments)
-			break;
-		t0 = now_sec();
-		rc = pread_full(job->fd, a, job->segment_sz, fpos);
-		t_read += now_sec() - t0;
-		if (rc)
-			break;
-		if (job->do_scan)
+		memset(&loc, 0, sizeof(loc));
+		pthread_barrier_wait(&job->gate);            /* pass start (the timer starts at the first) */
+		while (rc == 0)
 		{
-			t0 = now_sec();
-			ora_scan_pages(a, n_pages, (uint32_t)(fpos / ORA_BLCKSZ), NULL, &loc);
-			t_scan += now_sec() - t0;
-		}
-		if (job->do_compare)
-		{
-			uint64_t nm, fo;
+			uint64_t seg = __sync_fetch_and_add(&job->cursor, 1);
+			uint64_t fpos = seg * job->segment_sz;
+			uint64_t n_pages = job->segment_sz / ORA_BLCKSZ;
 
+			if (seg >= job->n_segments)
+				break;
 			t0 = now_sec();
-			rc = pread_full(job->fd, b, job->segment_sz, fpos);
+			rc = pread_full(job->fd, a, job->segment_sz, fpos);
+			t_read += now_sec() - t0;
 			if (rc)
 				break;
-			ora_verify_blocks(a, b, n_pages, NULL, &nm, &fo);
-			t_cmp += now_sec() - t0;
-			loc.v[ORA_T_MISMATCH_BLOCKS] += nm;
-			if (fo != ~(uint64_t)0 && fpos + fo < bad_first)
-				bad_first = fpos + fo;
+			if (job->do_scan)
+			{
+				t0 = now_sec();
+				ora_scan_pages(a, n_pages, (uint32_t)(fpos / ORA_BLCKSZ), NULL, &loc);
+				t_scan += now_sec() - t0;
+			}
+			if (job->do_compare)
+			{
+				uint64_t nm, fo;
+
+				t0 = now_sec();
+				rc = pread_full(job->fd, b, job->segment_sz, fpos);
+				if (rc)
+					break;
+				ora_verify_blocks(a, b, n_pages, NULL, &nm, &fo);
+				t_cmp += now_sec() - t0;
+				loc.v[ORA_T_MISMATCH_BLOCKS] += nm;
+				if (fo != ~(uint64_t)0 && fpos + fo < bad_first)
+					bad_first = fpos + fo;
+			}
 		}
+		pthread_barrier_wait(&job->gate);            /* everybody is done with this pass */
+		pthread_mutex_lock(&job->lock);
+		if (rc && !job->err)
+			job->err = rc;
+		if (pass == job->passes - 1)
+		{
+			for (int i = 0; i < ORA_T_COUNT; i++)
+			{
+				if (i == ORA_T_XOR_CHECKSUM)
+					job->totals.v[i] ^= loc.v[i];
+				else if (i != ORA_T_FIRST_MISMATCH)
+					job->totals.v[i] += loc.v[i];
+			}
+			if (bad_first < job->totals.v[ORA_T_FIRST_MISMATCH])
+				job->totals.v[ORA_T_FIRST_MISMATCH] = bad_first;
+		}
+		pthread_mutex_unlock(&job->lock);
+		pthread_barrier_wait(&job->gate);            /* the cursor has been reset for the next pass */
 	}
 	free(a);
 	free(b);
 	pthread_mutex_lock(&job->lock);
-	if (rc && !job->err)
-		job->err = rc;
-	for (int i = 0; i < ORA_T_COUNT; i++)
-	{
-		if (i == ORA_T_XOR_CHECKSUM)
-			job->totals.v[i] ^= loc.v[i];
-		else if (i != ORA_T_FIRST_MISMATCH)
-			job->totals.v[i] += loc.v[i];
-	}
-	if (bad_first < job->totals.v[ORA_T_FIRST_MISMATCH])
-		job->totals.v[ORA_T_FIRST_MISMATCH] = bad_first;
 	job->t_read += t_read;
 	job->t_scan += t_scan;
 	job->t_cmp += t_cmp;
@@ -720,17 +744,17 @@ static void *cpu_worker(void *arg)
 	return NULL;
 }
 
-int ora_cpu_path(const char *path, uint64_t segment_sz, uint64_t max_bytes,
-				 int n_threads, int do_scan, int do_compare,
-				 ora_totals *totals, double seconds[4])
+int ora_cpu_path_passes(const char *path, uint64_t segment_sz, uint64_t max_bytes,
+						int n_threads, int do_scan, int do_compare, int passes,
+						ora_totals *totals, double seconds[4])
 {
 	cpu_job job;
 	pthread_t *th;
 	off_t fsize;
-	double t0;
+	double t0 = 0, wall = 0;
 	int i;
 
-	if (n_threads < 1 || segment_sz == 0 || segment_sz % ORA_BLCKSZ)
+	if (n_threads < 1 || passes < 1 || segment_sz == 0 || segment_sz % ORA_BLCKSZ)
 		return -EINVAL;
 	memset(&job, 0, sizeof(job));
 	job.fd = open(path, O_RDONLY);
@@ -743,22 +767,41 @@ int ora_cpu_path(const char *path, uint64_t segment_sz, uint64_t max_bytes,
 	job.n_segments = (uint64_t)fsize / segment_sz;      /* tail dropped, nvme_test.c:785 */
 	job.do_scan = do_scan;
 	job.do_compare = do_compare;
+	job.passes = passes;
+	job.n_threads = n_threads;
 	job.totals.v[ORA_T_FIRST_MISMATCH] = ~(uint64_t)0;
 	pthread_mutex_init(&job.lock, NULL);
+	pthread_barrier_init(&job.gate, NULL, (unsigned)n_threads + 1);
 	th = calloc((size_t)n_threads, sizeof(*th));
-	t0 = now_sec();
 	for (i = 0; i < n_threads; i++)
 		pthread_create(&th[i], NULL, cpu_worker, &job);
+	for (int pass = 0; pass < passes; pass++)
+	{
+		pthread_barrier_wait(&job.gate);                /* buffers exist and are touched: go */
+		t0 = now_sec();
+		pthread_barrier_wait(&job.gate);                /* pass done */
+		wall += now_sec() - t0;
+		job.cursor = 0;
+		pthread_barrier_wait(&job.gate);
+	}
 	for (i = 0; i < n_threads; i++)
 		pthread_join(th[i], NULL);
-	seconds[3] = now_sec() - t0;
-	seconds[0] = job.t_read / n_threads;
-	seconds[1] = job.t_scan / n_threads;
-	seconds[2] = job.t_cmp / n_threads;
+	seconds[3] = wall / passes;                         /* per pass */
+	seconds[0] = job.t_read / n_threads / passes;
+	seconds[1] = job.t_scan / n_threads / passes;
+	seconds[2] = job.t_cmp / n_threads / passes;
 	free(th);
 	close(job.fd);
 	pthread_mutex_destroy(&job.lock);
+	pthread_barrier_destroy(&job.gate);
 	if (totals)
 		*totals = job.totals;
 	return job.err;
+}
+
+int ora_cpu_path(const char *path, uint64_t segment_sz, uint64_t max_bytes,
+				 int n_threads, int do_scan, int do_compare,
+				 ora_totals *totals, double seconds[4])
+{
+	return ora_cpu_path_passes(path, segment_sz, max_bytes, n_threads, do_scan, do_compare, 1, totals, seconds);
 }

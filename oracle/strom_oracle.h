@@ -140,6 +140,13 @@ int ora_plan_chunks(int to_gpu, uint32_t nr_chunks, uint32_t chunk_sz,
 int ora_cpu_path(const char *path, uint64_t segment_sz, uint64_t max_bytes,
 				 int n_threads, int do_scan, int do_compare,
 				 ora_totals *totals, double seconds[4]);
+/* the same over `passes` passes with the workers and their segment buffers kept
+ * across them; buffers are allocated and touched before the timer starts (the
+ * reference allocates once at start-up, utils/nvme_test.c:276-323).
+ * seconds[] are per-pass averages; totals are those of the last pass.         */
+int ora_cpu_path_passes(const char *path, uint64_t segment_sz, uint64_t max_bytes,
+						int n_threads, int do_scan, int do_compare, int passes,
+						ora_totals *totals, double seconds[4]);
 
 #ifdef __cplusplus
 }

@@ -67,6 +67,8 @@ class Oracle:
                                       C.c_void_p]
         o.ora_cpu_path.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int,
                                    C.c_void_p, C.POINTER(C.c_double)]
+        o.ora_cpu_path_passes.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int,
+                                          C.c_void_p, C.POINTER(C.c_double)]
         self.lib = o
 
     # ---- helpers returning numpy ----

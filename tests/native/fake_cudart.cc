@@ -179,4 +179,26 @@ cudaError_t CUDARTAPI cudaEventSynchronize(cudaEvent_t e)
 	return cudaSuccess;
 }
 
+cudaError_t CUDARTAPI cudaEventQuery(cudaEvent_t e)
+{
+	FakeEvent *ev = reinterpret_cast<FakeEvent *>(e);
+	std::lock_guard<std::mutex> g(ev->m);
+	return ev->completed >= ev->recorded ? cudaSuccess : cudaErrorNotReady;
+}
+
+cudaError_t CUDARTAPI cudaEventDestroy(cudaEvent_t e)
+{
+	delete reinterpret_cast<FakeEvent *>(e);
+	return cudaSuccess;
+}
+
+/* the fake stream's thread is detached and idles forever: nothing to take down */
+cudaError_t CUDARTAPI cudaStreamDestroy(cudaStream_t) { return cudaSuccess; }
+
+cudaError_t CUDARTAPI cudaFreeHost(void *p)
+{
+	free(p);
+	return cudaSuccess;
+}
+
 } /* extern "C" */

@@ -8,6 +8,7 @@
  *
  * usage: gpu_pipeline_san <file> <mode>      mode: load | fault | pinned (file on tmpfs:
  *        nvme_strom_pin_file first, so pieces are long and copied straight from the mapping)
+ *        | reconf (strom_debug_reconfigure between loads)
  */
 #include <atomic>
 #include <cerrno>
@@ -157,6 +158,54 @@ int main(int argc, char **argv)
 		CHECK(nvme_strom_ioctl(STROM_IOCTL__MEMCPY_WAIT, &wt) == 0);
 		CHECK(memcmp(win, want.data() + (size_t)7168 * 8192, (size_t)2048 * 8192) == 0);
 		CHECK(fake_copy_count() - before <= 3);
+	}
+
+	/* the engine's own decisions: a fixed reader count is kept; a self-adjusting one stays inside
+	 * [2, readers] and is accounted for (the fake link is as fast as memory, so the readers are
+	 * always the slow side and the count can only have grown) */
+	{
+		StromEngineState es;
+		CHECK(strom_debug_engine_state(0, &es) == 0);
+		CHECK(es.readers >= 1 && es.readers_active >= 1 && es.readers_active <= es.readers);
+		CHECK(es.slots_starved <= es.slots_staged);
+		if (getenv("NVME_STROM_READERS"))
+			CHECK(!es.adaptive && es.grown == 0 && es.shrunk == 0 && es.readers == atoi(getenv("NVME_STROM_READERS")));
+		else
+			CHECK(es.adaptive && es.readers_active >= 2 && es.readers == es.readers_max);
+		fprintf(stderr, "engine: cpus %d readers %d active %d grown %llu shrunk %llu starved %llu of %llu slots\n",
+				es.allowed_cpus, es.readers, es.readers_active, (unsigned long long)es.grown,
+				(unsigned long long)es.shrunk, (unsigned long long)es.slots_starved, (unsigned long long)es.slots_staged);
+	}
+	/* tuning hook: new staging geometry in the same process; refused while a task is in flight */
+	if (!strcmp(argv[2], "reconf"))
+	{
+		std::vector<uint32_t> ids(2048);
+		for (uint32_t k = 0; k < 2048; k++)
+			ids[k] = 100 + k;
+		for (int round = 0; round < 2; round++)
+		{
+			setenv("NVME_STROM_SLOT_KB", round ? "4096" : "512", 1);
+			setenv("NVME_STROM_SLOTS", round ? "4" : "3", 1);
+			CHECK(strom_debug_reconfigure() == 0);
+			StromEngineState es;
+			(void)strom_debug_engine_state(0, &es);
+			CHECK(es.slot_bytes == (round ? 4096u : 512u) << 10 && es.slots == (round ? 4 : 3));
+			StromCmd__MemCopySsdToGpu cp;
+			memset(&cp, 0, sizeof(cp));
+			cp.handle = mg.handle;
+			cp.file_desc = fd;
+			cp.nr_chunks = 2048;
+			cp.chunk_sz = 8192;
+			cp.chunk_ids = ids.data();
+			CHECK(nvme_strom_ioctl(STROM_IOCTL__MEMCPY_SSD2GPU, &cp) == 0);
+			int busy = strom_debug_reconfigure();                     /* most likely still in flight */
+			CHECK(busy == 0 || errno == EBUSY);
+			StromCmd__MemCopyWait wt;
+			memset(&wt, 0, sizeof(wt));
+			wt.dma_task_id = cp.dma_task_id;
+			CHECK(nvme_strom_ioctl(STROM_IOCTL__MEMCPY_WAIT, &wt) == 0 && wt.status == 0);
+			CHECK(memcmp(win, want.data() + (size_t)100 * 8192, (size_t)2048 * 8192) == 0);
+		}
 	}
 
 	/* UNMAP with a task still in flight has to wait for it (pmemmap.c:172-193) */

@@ -33,6 +33,20 @@ def test_reference_arm_line():
     assert cb["kind"] in ("port", "reference") and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["gpu_launches"] == 0
+    assert set(cb["phases_per_pass_s"]) == {"read_s", "scan_s", "compare_s", "wall_s"}
+
+
+def test_reference_arm_maps_no_product_library():
+    """the reference arm is the reference's CPU path and nothing else: the process that times it never
+    loads libnvme_strom (its file comes from the oracle's own generator)"""
+    code = (f"import sys, runpy; sys.argv = ['bench.py', '--impl', 'reference', '--steps', '1', '--warmup', '0'];\n"
+            f"try:\n    runpy.run_path({BENCH!r}, run_name='__main__')\nexcept SystemExit: pass\n"
+            "maps = open('/proc/self/maps').read()\n"
+            "assert 'libstrom_oracle.so' in maps\n"
+            "assert 'libnvme_strom' not in maps, [l for l in maps.splitlines() if 'libnvme_strom' in l]\n"
+            "print('CLEAN')")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "CLEAN" in r.stdout, r.stdout[-1500:] + r.stderr[-3000:]
 
 
 def test_reference_arm_other_ranks_stay_silent():

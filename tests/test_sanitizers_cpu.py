@@ -35,7 +35,12 @@ def test_host_pipeline_under_sanitizer(tmp_path, san):
 
 GPU_MODES = [("load", {}), ("load", {"NVME_STROM_SLOTS": "2", "NVME_STROM_SLOT_KB": "128", "NVME_STROM_SUB_KB": "64"}),
              ("fault", {"NVME_STROM_FAULT_EVERY": "7"}), ("pinned", {"NVME_STROM_SLOT_KB": "1024"}),
-             ("load", {"NVME_STROM_COPY": "nta"}), ("load", {"NVME_STROM_COPY": "ntstore"})]
+             ("load", {"NVME_STROM_COPY": "nta"}), ("load", {"NVME_STROM_COPY": "ntstore"}),
+             # self-adjusting reader count (no NVME_STROM_READERS), on its own and with a tiny ring
+             ("load", {"NVME_STROM_READERS": None}),
+             ("load", {"NVME_STROM_READERS": None, "NVME_STROM_SLOTS": "2", "NVME_STROM_SLOT_KB": "128", "NVME_STROM_SUB_KB": "64"}),
+             ("fault", {"NVME_STROM_READERS": None, "NVME_STROM_FAULT_EVERY": "5"}),
+             ("reconf", {}), ("reconf", {"NVME_STROM_READERS": None})]
 
 
 @pytest.mark.parametrize("san", ["thread", "address,undefined"])
@@ -59,7 +64,9 @@ def test_gpu_engine_model_under_sanitizer(tmp_path, san):
             d = "/dev/shm"
         path = os.path.join(d, f"gpu_san_{os.getpid()}.heap")
         env = dict(os.environ, TSAN_OPTIONS="halt_on_error=1 second_deadlock_stack=1", ASAN_OPTIONS="detect_leaks=0",
-                   UBSAN_OPTIONS="halt_on_error=1", NVME_STROM_READERS="4", **extra)
+                   UBSAN_OPTIONS="halt_on_error=1", NVME_STROM_READERS="4")
+        env.update(extra)
+        env = {k: v for k, v in env.items() if v is not None}
         try:
             r = subprocess.run([exe, path, mode], env=env, capture_output=True, text=True, timeout=600)
         finally:
