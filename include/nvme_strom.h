@@ -246,6 +246,27 @@ int nvme_strom_pin_file_range(int fdesc, uint64_t offset, uint64_t length);
  * Returns 0, or -1/errno when fdesc is not an open file. */
 int nvme_strom_unpin_file(int fdesc);
 
+/*
+ * Striped sources: one logical block range spread over several files, the user-space form of
+ * the md-RAID0 arrays the module reads from (kmod/nvme_strom.c:736-820 strom_raid0_map_sector,
+ * applied per page at :1350-1362).  Byte L of the set lives in member m at offset o by the
+ * module's arithmetic: chunk c = L / stripe_bytes, m = c mod M, o = (c div M) * stripe_bytes +
+ * L mod stripe_bytes for members of equal size; members of unequal size form further zones the
+ * way md lays them out.  One member per device or mount point is how the source side of one GPU
+ * gets the bandwidth of several.
+ *
+ * nvme_strom_stripe_open() returns a TOKEN descriptor that stands for the set wherever the
+ * ioctl API takes a file: `fdesc` of CHECK_FILE, `file_desc` of MEMCPY_SSD2GPU / MEMCPY_SSD2RAM
+ * (chunk ids, relseg_sz, counters and errors mean what they mean for one file; fstat() on the
+ * token reports the set's logical size).  The library keeps its own references on the members:
+ * the caller may close them.  stripe_bytes: multiple of 4096; member sizes are used in whole
+ * stripes.  A request never merges across members (:1370), so nr_dma_submit counts per-member
+ * requests.  Returns the token, or -1/errno (EINVAL, EBADF, EACCES, ENOTSUPP for a non-file).
+ * nvme_strom_stripe_close() forgets the set and closes the token; transfers in flight finish.
+ */
+int nvme_strom_stripe_open(const int *member_fds, unsigned int n_members, uint64_t stripe_bytes);
+int nvme_strom_stripe_close(int token);
+
 /* The text the proc entry returns on read(2) (kmod/nvme_strom.c:2036-2061).
  * Copies at most len bytes, returns the number copied. */
 size_t nvme_strom_version(char *buf, size_t len);

@@ -30,6 +30,21 @@ int strom_plan_chunks_debug(int to_gpu, uint32_t nr_chunks, uint32_t chunk_sz, u
 							uint32_t piece_max, uint32_t *counters, uint32_t *ids_out,
 							uint64_t *pieces, uint32_t max_pieces, uint32_t *n_pieces);
 
+/* The stripe-set mapping on explicit inputs (no files): where logical [logical, +len) of a set
+ * of n_members members of member_bytes[] bytes and stripe_bytes per chunk lives.  *set_bytes = the
+ * set's logical size.  0, or -EINVAL (bad geometry), -ESPIPE (crosses a chunk), -ERANGE (outside). */
+int strom_stripe_map_debug(const uint64_t *member_bytes, uint32_t n_members, uint64_t stripe_bytes,
+						   uint64_t logical, uint32_t len, uint32_t *member, uint64_t *member_off,
+						   uint64_t *set_bytes);
+
+/* strom_plan_chunks_debug() for a stripe set: pieces come back as quadruples
+ * {member_off, dest_off, length, member}. */
+int strom_plan_chunks_striped_debug(int to_gpu, uint32_t nr_chunks, uint32_t chunk_sz, uint32_t relseg_sz,
+									const uint32_t *chunk_ids, const uint64_t *member_bytes, uint32_t n_members,
+									uint64_t stripe_bytes, uint64_t dest_offset, uint64_t dest_length,
+									uint64_t dest_segment_sz, uint32_t piece_max, uint32_t *counters,
+									uint32_t *ids_out, uint64_t *pieces, uint32_t max_pieces, uint32_t *n_pieces);
+
 /* FIEMAP view of an open file as the planner sees it: triples {logical,
  * physical, length}; returns the number of extents (0 = identity map), or -errno */
 int strom_file_extents_debug(int fd, uint64_t *extents, uint32_t max_extents);

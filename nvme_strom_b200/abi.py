@@ -122,6 +122,10 @@ lib.nvme_strom_close.argtypes = [C.c_int]
 lib.nvme_strom_pin_file.argtypes = [C.c_int]
 lib.nvme_strom_pin_file_range.argtypes = [C.c_int, C.c_uint64, C.c_uint64]
 lib.nvme_strom_unpin_file.argtypes = [C.c_int]
+lib.nvme_strom_stripe_open.argtypes = [C.POINTER(C.c_int), C.c_uint, C.c_uint64]
+lib.nvme_strom_stripe_close.argtypes = [C.c_int]
+lib.strom_stripe_map_debug.argtypes = [C.POINTER(C.c_uint64), C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32,
+                                       C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
 lib.strom_debug_pagecache_read.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
 
 

@@ -156,6 +156,36 @@ static int open_direct_twin(int fd)
 	return open(path, O_RDONLY | O_DIRECT | O_CLOEXEC);
 }
 
+/* a stripe set's member fd for reading: the buffered dup, or its O_DIRECT twin (opened once) */
+static int stripe_member_fd(StripeSet &set, uint32_t member, bool direct)
+{
+	if (!direct)
+		return set.fds[member];
+	std::lock_guard<std::mutex> g(set.lock);
+	if (set.fds_direct[member] < 0)
+		set.fds_direct[member] = open_direct_twin(set.fds[member]);
+	return set.fds_direct[member] >= 0 ? set.fds_direct[member] : set.fds[member];
+}
+
+/* the mapped views a task reads from: one for a plain file, one per member for a stripe set
+ * (entries may be null: that source is read with pread) */
+static void attach_sources(DmaTask *task, int own_fd, const struct stat &st, const std::shared_ptr<StripeSet> &stripe)
+{
+	task->stripe = stripe;
+	if (!stripe)
+	{
+		task->sources.assign(1, want_direct_io() ? nullptr : source_map_get(own_fd, st));
+		return;
+	}
+	task->sources.assign(stripe->fds.size(), nullptr);
+	for (size_t m = 0; m < stripe->fds.size() && !want_direct_io(); m++)
+	{
+		struct stat mst;
+		if (fstat(stripe->fds[m], &mst) == 0)
+			task->sources[m] = source_map_get(stripe->fds[m], mst);
+	}
+}
+
 static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 {
 	if (arg->nr_chunks > 0 && !arg->chunk_ids)
@@ -171,12 +201,16 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 	int rc = check_source_file(arg->file_desc, &st);      /* strom_create_dma_task :595-611 */
 	if (rc)
 		return rc;
+	/* a stripe-set token stands for several member files (stripe.cc); its size is the set's */
+	std::shared_ptr<StripeSet> stripe = stripe_set_of(st);
 	FileInfo finfo;
-	if ((rc = cached_file_info(arg->file_desc, st, &finfo)) != 0)
+	if (stripe)
+		finfo.size = stripe->map.size;
+	else if ((rc = cached_file_info(arg->file_desc, st, &finfo)) != 0)
 		return rc;
 
 	std::vector<uint8_t> state;
-	const bool split = want_cache_split() && arg->wb_buffer != nullptr;
+	const bool split = want_cache_split() && arg->wb_buffer != nullptr && !stripe;
 	if (split && (rc = build_page_state(arg->file_desc, arg->nr_chunks, arg->chunk_sz, arg->relseg_sz,
 										arg->chunk_ids, finfo.size, &state)) != 0)
 		return rc;
@@ -196,7 +230,8 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 	/* the mapped view of the source (null: pread).  Where the source is already page-locked
 	 * (tmpfs, after the background locking has caught up) no staging is needed, so the pieces
 	 * can be as long as the request is contiguous. */
-	std::shared_ptr<SourceMap> source = want_direct_io() ? nullptr : source_map_get(arg->file_desc, st);
+	std::shared_ptr<SourceMap> source = (want_direct_io() || stripe) ? nullptr : source_map_get(arg->file_desc, st);
+	in.stripe = stripe ? &stripe->map : nullptr;
 	const uint64_t req_bytes = (uint64_t)arg->nr_chunks * arg->chunk_sz;
 	const uint64_t first_fpos = arg->nr_chunks ? (uint64_t)(arg->relseg_sz ? arg->chunk_ids[0] % arg->relseg_sz
 																			 : arg->chunk_ids[0]) * arg->chunk_sz : 0;
@@ -217,10 +252,12 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 		return -errno;
 	DmaTask *task = task_create(session, own_fd, win);
 	unref.armed = false;                                   /* the task owns the ref now */
-	if (want_direct_io())
+	if (want_direct_io() && !stripe)
 		task->fd_direct = open_direct_twin(own_fd);
+	if (stripe)
+		attach_sources(task, own_fd, st, stripe);
 	else
-		task->source = source;
+		task->sources.assign(1, source);
 	const unsigned long task_id = task->id;
 
 	/* chunks that are mostly in the page cache come back through wb_buffer,
@@ -244,10 +281,11 @@ static int do_memcpy_ssd2gpu(int session, StromCmd__MemCopySsdToGpu *arg)
 	{
 		std::vector<Job> jobs;
 		jobs.reserve(plan.pieces.size());
-		const bool direct = task->fd_direct >= 0;
+		const bool direct = stripe ? want_direct_io() : task->fd_direct >= 0;
 		for (const Piece &p : plan.pieces)
-			jobs.push_back({task, direct ? task->fd_direct : own_fd, direct, p.file_off, p.length,
-							reinterpret_cast<char *>(win->map_address + p.dest_off), task->source.get()});
+			jobs.push_back({task, stripe ? stripe_member_fd(*stripe, p.member, direct) : (direct ? task->fd_direct : own_fd),
+							direct, p.file_off, p.length,
+							reinterpret_cast<char *>(win->map_address + p.dest_off), task->sources[p.member].get(), p.member});
 		task_add_ref(task, (int)jobs.size());
 		engine_submit(engine_for_window(*win), jobs);
 	}
@@ -283,11 +321,14 @@ static int do_memcpy_ssd2ram(int session, StromCmd__MemCopySsdToRam *arg)
 	struct stat st;
 	if ((rc = check_source_file(arg->file_desc, &st)) != 0)
 		return rc;
+	std::shared_ptr<StripeSet> stripe = stripe_set_of(st);
 	FileInfo finfo;
-	if ((rc = cached_file_info(arg->file_desc, st, &finfo)) != 0)
+	if (stripe)
+		finfo.size = stripe->map.size;
+	else if ((rc = cached_file_info(arg->file_desc, st, &finfo)) != 0)
 		return rc;
 	std::vector<uint8_t> state;
-	const bool split = want_cache_split();
+	const bool split = want_cache_split() && !stripe;
 	if (split && (rc = build_page_state(arg->file_desc, arg->nr_chunks, arg->chunk_sz, arg->relseg_sz,
 										arg->chunk_ids, finfo.size, &state)) != 0)
 		return rc;
@@ -305,6 +346,7 @@ static int do_memcpy_ssd2ram(int session, StromCmd__MemCopySsdToRam *arg)
 	in.page_state = split ? state.data() : nullptr;
 	in.n_state_pages = state.size();
 	in.piece_max = engine_piece_max();
+	in.stripe = stripe ? &stripe->map : nullptr;
 	Plan plan;
 	if ((rc = plan_chunks(in, &plan)) != 0)
 		return rc;
@@ -319,7 +361,7 @@ static int do_memcpy_ssd2ram(int session, StromCmd__MemCopySsdToRam *arg)
 	if (own_fd < 0)
 		return -errno;
 	DmaTask *task = task_create(session, own_fd, nullptr);
-	task->source = source_map_get(own_fd, st);
+	attach_sources(task, own_fd, st, stripe);
 	const unsigned long task_id = task->id;
 	char *base = static_cast<char *>(arg->dest_uaddr) - buf_off;   /* address of buffer offset 0 */
 
@@ -342,7 +384,8 @@ static int do_memcpy_ssd2ram(int session, StromCmd__MemCopySsdToRam *arg)
 		std::vector<Job> jobs;
 		jobs.reserve(plan.pieces.size());
 		for (const Piece &p : plan.pieces)
-			jobs.push_back({task, own_fd, false, p.file_off, p.length, base + p.dest_off, task->source.get()});
+			jobs.push_back({task, stripe ? stripe_member_fd(*stripe, p.member, false) : own_fd, false, p.file_off, p.length,
+							base + p.dest_off, task->sources[p.member].get(), p.member});
 		task_add_ref(task, (int)jobs.size());
 		engine_submit(engine_for_host(), jobs);
 	}

@@ -766,13 +766,15 @@ private:
 	}
 
 	/*
-	 * How many readers take part (lock held).  Evidence is gathered over windows of 16 staged
+	 * How many readers take part (lock held).  Evidence is gathered over windows of 64 staged
 	 * slots: a slot counts as starved when it was queued behind a finished copy although more
-	 * pieces were waiting -- the readers, not the link, set the pace.  A quarter of a window
-	 * starved lets one more reader in; eight windows in a row without a single starved slot let
-	 * one go.  When letting one go is answered by starvation at once, the count goes back up and
-	 * stays put for a while that doubles every time (the link-bound point has been found; there
-	 * is no reason to keep probing it).
+	 * pieces were waiting -- the readers, not the link, set the pace.  Measured on B200 (profiles/
+	 * r02_ring_n1.txt): at the link-bound reader count about 0.3 % of the slots are starved, one
+	 * reader short of it 5 %, two short 40 %.  So: two or more starved slots in a window (3 %) let
+	 * one more reader in -- two more when a quarter of the window starved; eight windows in a row
+	 * without any let one go.  When letting one go is answered by starvation within two windows,
+	 * the count goes back up and stays put for a while that doubles every time (the link-bound
+	 * point has been found; there is no reason to keep probing it).
 	 */
 	void account_slot(bool starved)
 	{
@@ -784,15 +786,17 @@ private:
 		win_issued_++;
 		if (starved)
 			win_starved_++;
-		if (win_issued_ < 16)
+		if (win_issued_ < 64)
 			return;
 		const int max = (int)threads_.size();
-		if (win_starved_ * 4 >= win_issued_)
+		if (win_starved_ >= 2)
 		{
-			if (active_ < max)
+			const int step = win_starved_ * 4 >= win_issued_ ? 2 : 1;
+			const int to = std::min(max, active_ + step);
+			if (to > active_)
 			{
-				active_++;
-				n_grown_++;
+				n_grown_ += (uint64_t)(to - active_);
+				active_ = to;
 				park_cv_.notify_all();
 			}
 			if (since_shrink_ <= 2)                   /* that reader was needed */
@@ -962,14 +966,20 @@ private:
 				ring_next_ = (ring_next_ + 1) % (int)stages_.size();
 				Job j = queue_.front();
 				queue_.pop_front();
-				n.backlog = !queue_.empty();
+				/* more pieces waiting AND the ring already at work: only then does a link found
+				 * idle say anything about the readers (the first piece after a pause always finds
+				 * it idle) */
+				bool ring_busy = false;
+				for (const Stage &other : stages_)
+					ring_busy = ring_busy || (&other != &n && other.state != kFree);
+				n.backlog = !queue_.empty() && (ring_busy || was_in_flight);
 				n.state = kPreparing;
 				open_ = idx;
 				g.unlock();
 				if (was_in_flight)
 					retire_stage(n);
 				const bool from_source = j.src && !j.direct && !g_skip_h2d.load(std::memory_order_relaxed) &&
-										 j.task->source->region_ready(j.file_off, j.length, j.task->source, device_);
+										 j.task->sources[j.member]->region_ready(j.file_off, j.length, j.task->sources[j.member], device_);
 				if (from_source)
 				{
 					/* page-locked source (tmpfs): the copy engine reads the page cache itself; the
@@ -1069,7 +1079,7 @@ private:
 	std::condition_variable cv_;
 	std::condition_variable park_cv_;     /* readers beyond active_ wait here      */
 	int active_ = 1;                      /* readers taking part                   */
-	uint32_t win_issued_ = 0, win_starved_ = 0, calm_ = 0, hold_ = 0, hold_next_ = 16, since_shrink_ = 1000;
+	uint32_t win_issued_ = 0, win_starved_ = 0, calm_ = 0, hold_ = 0, hold_next_ = 32, since_shrink_ = 1000;
 	uint64_t n_grown_ = 0, n_shrunk_ = 0, n_starved_ = 0, n_issued_ = 0;
 	std::deque<Job> queue_;
 	std::condition_variable ready_cv_;

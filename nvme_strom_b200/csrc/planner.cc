@@ -71,9 +71,10 @@ int plan_chunks(const PlanInput &in, Plan *out)
 	out->pieces.clear();
 	out->cached.clear();
 
-	/* the module's pending request, in sectors of the physical address */
+	/* the module's pending request, in sectors of the physical address (and, for a stripe set,
+	 * on one member: dtask->nvme_ns == nvme_ns at kmod/nvme_strom.c:1370) */
 	uint64_t req_sector = 0, req_dest = 0;
-	uint32_t req_nr = 0;
+	uint32_t req_nr = 0, req_member = 0;
 	auto flush_request = [&] {
 		if (req_nr > 0)
 		{
@@ -83,7 +84,7 @@ int plan_chunks(const PlanInput &in, Plan *out)
 		}
 	};
 	/* our own pending transfer piece */
-	Piece piece = {0, 0, 0};
+	Piece piece = {0, 0, 0, 0};
 	auto flush_piece = [&] {
 		if (piece.length > 0)
 			out->pieces.push_back(piece);
@@ -125,12 +126,26 @@ int plan_chunks(const PlanInput &in, Plan *out)
 			uint64_t curr = dest;
 			for (uint32_t j = 0; j < nr_pages; j++, curr += kPageSz)
 			{
-				uint64_t phys;
-				if (!physical_of(*in.file, fpos + (uint64_t)j * kPageSz, &phys, &hint))
+				const uint64_t lpos = fpos + (uint64_t)j * kPageSz;
+				uint64_t phys = 0, mpos = lpos;
+				uint32_t member = 0;
+				if (in.stripe)
+				{
+					/* array position -> member and position in it, page by page (:1350-1362);
+					 * a member file is taken as its own device: position == "sector" */
+					const int mrc = in.stripe->map(lpos, kPageSz, &member, &mpos);
+					if (mrc == -ERANGE && lpos >= in.file->size)
+						mpos = ~0ull - kPageSz;            /* tail of a chunk straddling the end: zeros */
+					else if (mrc != 0)
+						return mrc;
+					phys = mpos;
+				}
+				else if (!physical_of(*in.file, lpos, &phys, &hint))
 					phys = ~0ull - kPageSz;            /* hole: never merges, still read as zeros */
 				const uint64_t sector = phys / kSectorSz;
 				const uint32_t nsec = kPageSz / kSectorSz;
 				if (req_nr > 0 && req_nr + nsec <= max_sects && req_sector + req_nr == sector &&
+					req_member == member &&
 					req_dest + (uint64_t)kSectorSz * req_nr == curr &&
 					(in.dest_segment_sz == 0 ||
 					 curr / in.dest_segment_sz == (curr + kPageSz - 1) / in.dest_segment_sz))
@@ -140,18 +155,34 @@ int plan_chunks(const PlanInput &in, Plan *out)
 					flush_request();
 					req_dest = curr;
 					req_sector = sector;
+					req_member = member;
 					req_nr = nsec;
+				}
+				if (in.stripe)
+				{
+					/* transfer pieces of a stripe set grow page by page: a chunk may end inside
+					 * a request's chunk_sz */
+					if (piece.length > 0 && piece.member == member && piece.file_off + piece.length == mpos &&
+						piece.dest_off + piece.length == curr && piece.length + kPageSz <= in.piece_max)
+						piece.length += kPageSz;
+					else
+					{
+						flush_piece();
+						piece = {mpos, curr, kPageSz, member};
+					}
 				}
 			}
 			/* transfer piece: file- and destination-contiguous, <= piece_max */
-			if (piece.length > 0 && piece.file_off + piece.length == fpos &&
+			if (in.stripe)
+				;
+			else if (piece.length > 0 && piece.file_off + piece.length == fpos &&
 				piece.dest_off + piece.length == dest &&
 				piece.length + in.chunk_sz <= in.piece_max)
 				piece.length += in.chunk_sz;
 			else
 			{
 				flush_piece();
-				piece = {fpos, dest, in.chunk_sz};
+				piece = {fpos, dest, in.chunk_sz, 0};
 			}
 			if (in.to_gpu)
 			{
@@ -295,6 +326,54 @@ extern "C" int strom_plan_chunks_debug(int to_gpu, uint32_t nr_chunks, uint32_t 
 		pieces[3 * i] = plan.pieces[i].file_off;
 		pieces[3 * i + 1] = plan.pieces[i].dest_off;
 		pieces[3 * i + 2] = plan.pieces[i].length;
+	}
+	return 0;
+}
+
+extern "C" int strom_plan_chunks_striped_debug(int to_gpu, uint32_t nr_chunks, uint32_t chunk_sz, uint32_t relseg_sz,
+											   const uint32_t *chunk_ids, const uint64_t *member_bytes, uint32_t n_members,
+											   uint64_t stripe_bytes, uint64_t dest_offset, uint64_t dest_length,
+											   uint64_t dest_segment_sz, uint32_t piece_max, uint32_t *counters,
+											   uint32_t *ids_out, uint64_t *pieces, uint32_t max_pieces, uint32_t *n_pieces)
+{
+	StripeMap map;
+	int rc = stripe_map_build(member_bytes, n_members, stripe_bytes, &map);
+	if (rc)
+		return rc;
+	FileInfo fi;
+	fi.size = map.size;
+	PlanInput in = {};
+	in.to_gpu = to_gpu != 0;
+	in.nr_chunks = nr_chunks;
+	in.chunk_sz = chunk_sz;
+	in.relseg_sz = relseg_sz;
+	in.chunk_ids = chunk_ids;
+	in.dest_offset = dest_offset;
+	in.dest_length = dest_length;
+	in.dest_segment_sz = dest_segment_sz;
+	in.file = &fi;
+	in.piece_max = piece_max ? piece_max : engine_piece_max();
+	in.stripe = &map;
+	Plan plan;
+	if ((rc = plan_chunks(in, &plan)) != 0)
+		return rc;
+	if (counters)
+	{
+		counters[0] = plan.nr_cached;
+		counters[1] = plan.nr_direct;
+		counters[2] = plan.nr_dma_submit;
+		counters[3] = plan.nr_dma_blocks;
+	}
+	if (ids_out && to_gpu)
+		memcpy(ids_out, plan.ids_out.data(), sizeof(uint32_t) * nr_chunks);
+	if (n_pieces)
+		*n_pieces = (uint32_t)plan.pieces.size();
+	for (uint32_t i = 0; pieces && i < plan.pieces.size() && i < max_pieces; i++)
+	{
+		pieces[4 * i] = plan.pieces[i].file_off;
+		pieces[4 * i + 1] = plan.pieces[i].dest_off;
+		pieces[4 * i + 2] = plan.pieces[i].length;
+		pieces[4 * i + 3] = plan.pieces[i].member;
 	}
 	return 0;
 }

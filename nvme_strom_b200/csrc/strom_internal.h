@@ -86,6 +86,30 @@ struct SourceMap {
 };
 std::shared_ptr<SourceMap> source_map_get(int fd, const struct ::stat &st);   /* null: use pread */
 
+/* ---- striped sources (stripe.cc; kmod/nvme_strom.c:736-820) ----------------- */
+struct StripeZone {
+	uint64_t zone_end = 0;                /* logical end of the zone, bytes      */
+	uint64_t dev_start = 0;               /* where the zone starts in each member */
+	uint32_t nb_dev = 0;
+	std::vector<uint32_t> devs;           /* members taking part, in order       */
+};
+struct StripeMap {
+	uint64_t chunk_bytes = 0, size = 0;
+	uint32_t n_members = 0;
+	std::vector<StripeZone> zones;
+	/* logical [logical, +len) -> member file and offset; -ESPIPE across a chunk, -ERANGE outside */
+	int map(uint64_t logical, uint32_t len, uint32_t *member, uint64_t *member_off) const;
+};
+int stripe_map_build(const uint64_t *member_bytes, uint32_t n_members, uint64_t chunk_bytes, StripeMap *out);
+struct StripeSet {
+	StripeMap map;
+	std::vector<int> fds;                 /* our own dups of the members         */
+	std::vector<int> fds_direct;          /* O_DIRECT twins, opened on demand    */
+	std::mutex lock;                      /* fds_direct                          */
+	~StripeSet();
+};
+std::shared_ptr<StripeSet> stripe_set_of(const struct ::stat &token_st);    /* null: a plain file */
+
 /* ---- asynchronous tasks --------------------------------------------------- */
 struct DmaTask {
 	unsigned long id = 0;
@@ -95,7 +119,8 @@ struct DmaTask {
 	std::atomic<int>  pending{1};         /* 1 (creator) + pieces in flight     */
 	std::atomic<long> status{0};          /* first error wins, :680-686         */
 	std::shared_ptr<GpuWindow> window;    /* null for SSD2RAM                   */
-	std::shared_ptr<SourceMap> source;    /* null: read with pread              */
+	std::vector<std::shared_ptr<SourceMap>> sources;   /* per member (one for a plain file); null: pread */
+	std::shared_ptr<StripeSet> stripe;    /* null for a plain file              */
 	uint64_t      tsc_start = 0;
 };
 DmaTask *task_create(int session, int fd, std::shared_ptr<GpuWindow> win);
@@ -106,9 +131,10 @@ void task_session_closed(int session);
 
 /* ---- planner ---------------------------------------------------------------- */
 struct Piece {                            /* one pread + one copy                */
-	uint64_t file_off;
+	uint64_t file_off;                    /* in the member file for a stripe set */
 	uint64_t dest_off;                    /* bytes from window start / host base */
 	uint32_t length;
+	uint32_t member;                      /* 0 for a plain file                  */
 };
 struct Plan {
 	uint32_t nr_cached = 0, nr_direct = 0, nr_dma_submit = 0, nr_dma_blocks = 0;
@@ -131,6 +157,7 @@ struct PlanInput {
 	const uint8_t *page_state;            /* per 4KB file page, may be null      */
 	uint64_t    n_state_pages;
 	uint32_t    piece_max;                /* staging slot size                   */
+	const StripeMap *stripe;              /* null: `file` is one plain file      */
 };
 int plan_chunks(const PlanInput &in, Plan *out);          /* 0 or -errno         */
 int file_info_get(int fd, FileInfo *info, bool want_extents);
@@ -145,7 +172,8 @@ struct Job {
 	uint64_t file_off;
 	uint32_t length;
 	char    *dst;                         /* device or host address              */
-	const SourceMap *src;                 /* kept alive by task->source; may be null */
+	const SourceMap *src;                 /* kept alive by task->sources; may be null */
+	uint32_t member;                      /* index into task->sources            */
 };
 class Engine;
 Engine *engine_for_window(const GpuWindow &w);            /* created on demand   */

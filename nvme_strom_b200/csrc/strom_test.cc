@@ -532,7 +532,7 @@ static int print_gpu_memory(void)
 static void usage(const char *cmdname)
 {
 	fprintf(stderr,
-			"usage: %s [OPTIONS] <filename>\n"
+			"usage: %s [OPTIONS] <filename> [<member file> ... with -S]\n"
 			"    -d <device index>[,<index>...]: (default 0); several = shard the file over them\n"
 			"    -n <num of segments>:     (default 6)\n"
 			"    -s <segment size in MB>:  (default 32MB)\n"
@@ -540,7 +540,9 @@ static void usage(const char *cmdname)
 			"    -k : Checksum/validate the landed pages on the GPU (default off)\n"
 			"    -h : Print this message   (default off)\n"
 			"    -f([<i/o size in KB>]): Test by VFS access (default off)\n"
-			"    -p : Print property of mapped device memory\n",
+			"    -p : Print property of mapped device memory\n"
+			"    -S <stripe size in KB>: the files named are the members of a stripe set (RAID-0 layout),\n"
+			"                            read as one source (not with -f)\n",
 			basename(strdup(cmdname)));
 	exit(1);
 }
@@ -548,12 +550,13 @@ static void usage(const char *cmdname)
 int main(int argc, char *argv[])
 {
 	int c, fdesc;
+	long stripe_kb = 0;
 	struct stat stbuf;
 	std::vector<int> devices;
 
 	debug_trace = getenv("STROM_TEST_TRACE") != NULL;
 	setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);     /* slot streams + engine streams: avoid queue sharing */
-	while ((c = getopt(argc, argv, "d:n:s:ckpf::h")) >= 0)
+	while ((c = getopt(argc, argv, "d:n:s:S:ckpf::h")) >= 0)
 	{
 		switch (c)
 		{
@@ -563,6 +566,7 @@ int main(int argc, char *argv[])
 				break;
 			case 'n': nr_segments = atoi(optarg); break;
 			case 's': segment_sz = (size_t)atoi(optarg) << 20; break;
+			case 'S': stripe_kb = atol(optarg); break;
 			case 'c': enable_checks = 1; break;
 			case 'k': enable_scan = 1; break;
 			case 'p': print_mapping = 1; break;
@@ -592,7 +596,7 @@ int main(int argc, char *argv[])
 	CUDA_OK(cudaSetDevice(devices[0]));
 	if (print_mapping && optind == argc)
 		return print_gpu_memory();
-	if (optind + 1 != argc)
+	if (stripe_kb > 0 ? (optind >= argc || test_by_vfs) : optind + 1 != argc)
 		usage(argv[0]);
 	if (vfs_io_size == 0)
 		vfs_io_size = segment_sz;
@@ -601,7 +605,24 @@ int main(int argc, char *argv[])
 		fprintf(stderr, "VFS I/O size (%zuKB) mismatch to ChunkSize (%zuMB)\n", vfs_io_size >> 10, segment_sz >> 20);
 		return 1;
 	}
-	fdesc = open(argv[optind], O_RDONLY);
+	if (stripe_kb > 0)
+	{
+		/* the members of a stripe set, in order: one token descriptor stands for all of them
+		 * (the user-space form of the md-RAID0 case, kmod/nvme_strom.c:736-820) */
+		std::vector<int> members;
+		for (int i = optind; i < argc; i++)
+		{
+			int mfd = open(argv[i], O_RDONLY);
+			SYS_OK(mfd >= 0, "open member");
+			members.push_back(mfd);
+		}
+		fdesc = nvme_strom_stripe_open(members.data(), (unsigned int)members.size(), (uint64_t)stripe_kb << 10);
+		SYS_OK(fdesc >= 0, "nvme_strom_stripe_open");
+		for (int mfd : members)
+			close(mfd);
+	}
+	else
+		fdesc = open(argv[optind], O_RDONLY);
 	SYS_OK(fdesc >= 0, "open");
 	SYS_OK(fstat(fdesc, &stbuf) == 0, "fstat");
 	const uint64_t n_segs = (uint64_t)stbuf.st_size / segment_sz;               /* tail dropped, :785 */

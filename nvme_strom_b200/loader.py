@@ -180,17 +180,24 @@ class SegmentPipeline:
         """Loads segments [first_segment, first_segment + n_segments) and processes them on the
         GPU.  Returns (totals list, counters dict).
 
-        ``path`` is one file, or -- with ``relseg_sz`` > 0 -- the list of segment files of one
+        ``path`` is one file, a ``StripeSet`` (several member files read as one, RAID-0 layout:
+        kmod/nvme_strom.c:736-820), or -- with ``relseg_sz`` > 0 -- the list of segment files of one
         relation, each holding ``relseg_sz`` blocks (PostgreSQL: RELSEG_SIZE = 131072 blocks = 1 GB;
         block b lives in file b // relseg_sz at chunk b % relseg_sz, which is what the ioctl's
         relseg_sz does: kmod/nvme_strom.c:1524-1527; one fd per file as pgsql/nvme_strom.c:952-959).
         Block numbers, and with them the page checksums, stay relation-wide."""
-        paths = [path] if isinstance(path, str) else list(path)
+        if isinstance(path, StripeSet):
+            # a stripe set is one descriptor to the ioctl API; the caller keeps it open
+            paths, fds, borrowed = [], [os.dup(path.token)], True
+        else:
+            paths = [path] if isinstance(path, str) else list(path)
+            borrowed = False
         if len(paths) > 1 and relseg_sz <= 0:
             raise ValueError("several files need relseg_sz")
         if relseg_sz and relseg_sz % self.nr_chunks:
             raise ValueError("a pipeline segment must not straddle two relation files")
-        fds = [os.open(p, os.O_RDONLY) for p in paths]
+        if not borrowed:
+            fds = [os.open(p, os.O_RDONLY) for p in paths]
         fd = fds[0]
         try:
             carg = abi.StromCmd__CheckFile()
@@ -257,3 +264,54 @@ def partition_segments(n_segments, n_parts, rank):
     abi.check(lib.strom_partition_segments(n_segments, n_parts, rank, C.byref(first), C.byref(count)),
               "strom_partition_segments")
     return first.value, count.value
+
+
+def stripe_split(src_path, member_paths, stripe_bytes):
+    """Writes the RAID-0 members of a flat file: stripe chunk c of the source goes to member
+    c mod M at offset (c div M) * stripe_bytes (equal-sized members, the single-zone case of
+    kmod/nvme_strom.c:757-820).  The source size must be a multiple of M * stripe_bytes."""
+    m = len(member_paths)
+    size = os.path.getsize(src_path)
+    if size % (m * stripe_bytes):
+        raise ValueError("file size must be a multiple of members x stripe")
+    outs = [open(p, "wb") for p in member_paths]
+    try:
+        with open(src_path, "rb") as f:
+            c = 0
+            while True:
+                buf = f.read(stripe_bytes)
+                if not buf:
+                    break
+                outs[c % m].write(buf)
+                c += 1
+    finally:
+        for o in outs:
+            o.close()
+
+
+class StripeSet:
+    """A stripe set opened for the ioctl API: ``.token`` is the descriptor to pass as file_desc
+    (nvme_strom_stripe_open, include/nvme_strom.h)."""
+
+    def __init__(self, member_paths, stripe_bytes):
+        fds = [os.open(p, os.O_RDONLY) for p in member_paths]
+        try:
+            arr = (C.c_int * len(fds))(*fds)
+            self.token = lib.nvme_strom_stripe_open(arr, len(fds), stripe_bytes)
+            if self.token < 0:
+                abi.check(-1, "nvme_strom_stripe_open")
+        finally:
+            for f in fds:                                   # the library keeps its own references
+                os.close(f)
+        self.size = os.fstat(self.token).st_size
+
+    def close(self):
+        if self.token >= 0:
+            abi.check(lib.nvme_strom_stripe_close(self.token), "nvme_strom_stripe_close")
+            self.token = -1
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()

@@ -612,6 +612,49 @@ int ora_plan_chunks(int to_gpu, uint32_t nr_chunks, uint32_t chunk_sz,
 }
 
 /* ------------------------------------------------------------------ */
+/* md RAID-0 sector mapping                                            */
+/* kmod/nvme_strom.c:736-755 find_zone, :757-820 strom_raid0_map_sector */
+/* (mirrors drivers/md/raid0.c of the 3.10 kernel the module targets).  */
+/* Sectors are 512 bytes.  devlist is laid out as the module reads it:  */
+/* devlist[zone_index * raid_disks + k], raid_disks = zone[0].nb_dev.   */
+/* ------------------------------------------------------------------ */
+int ora_raid0_map_sector(const ora_strip_zone *zones, int nr_zones, const int *devlist,
+						 uint64_t chunk_sects, uint64_t *p_sector, uint32_t nr_sects, int *p_dev)
+{
+	uint64_t sector = *p_sector;
+	uint64_t sector_offset = sector;
+	uint64_t chunk;
+	uint64_t sect_in_chunk;
+	int raid_disks = (int)zones[0].nb_dev;
+	int zi;
+
+	/* :773-780 the i/o must not go across a chunk boundary */
+	if (sector / chunk_sects != (sector + nr_sects - 1) / chunk_sects)
+		return -ESPIPE;
+	/* :736-755 find_zone: first zone whose end lies beyond the sector; the offset becomes
+	 * relative to that zone's start */
+	for (zi = 0; zi < nr_zones; zi++)
+		if (sector < zones[zi].zone_end)
+		{
+			if (zi)
+				sector_offset = sector - zones[zi - 1].zone_end;
+			break;
+		}
+	if (zi == nr_zones)
+		return -ERANGE;                                 /* :783-788 */
+	/* :790-806 both branches (power-of-two chunk or not) compute the same quotients */
+	sect_in_chunk = sector % chunk_sects;
+	sector = sector / chunk_sects;                      /* absolute chunk number */
+	chunk = sector_offset / (chunk_sects * zones[zi].nb_dev);
+	sector_offset = chunk * chunk_sects + sect_in_chunk;
+	/* :812-818 member by absolute chunk number modulo the zone's width; data_offset and the
+	 * partition start are properties of real block devices and are 0 here */
+	*p_dev = devlist[zi * raid_disks + (int)(sector % zones[zi].nb_dev)];
+	*p_sector = sector_offset + zones[zi].dev_start;
+	return 0;
+}
+
+/* ------------------------------------------------------------------ */
 /* the reference's CPU path, config C1                                 */
 /* read loop utils/nvme_test.c:543-552; compare :249-266; the scan      */
 /* phase has no reference code (the oracle's own checksum/validate)     */

@@ -134,6 +134,14 @@ int ora_plan_chunks(int to_gpu, uint32_t nr_chunks, uint32_t chunk_sz,
 					uint32_t *chunk_ids_out, ora_run *runs, uint32_t max_runs,
 					ora_plan *plan);
 
+/* ---- md RAID-0: array sector -> (member, member sector), kmod/nvme_strom.c:736-820.
+ * zones[] as md keeps them (struct strip_zone: zone_end, dev_start in sectors, nb_dev);
+ * devlist[zone * zones[0].nb_dev + k] = member index.  0, -ESPIPE (crosses a chunk) or
+ * -ERANGE (outside the array).                                                   */
+typedef struct ora_strip_zone { uint64_t zone_end, dev_start; uint32_t nb_dev; } ora_strip_zone;
+int ora_raid0_map_sector(const ora_strip_zone *zones, int nr_zones, const int *devlist,
+						 uint64_t chunk_sects, uint64_t *p_sector, uint32_t nr_sects, int *p_dev);
+
 /* ---- the reference's CPU path (config C1): read + checksum/validate + compare
  * n_threads workers over disjoint segment ranges.  seconds[] = {read, scan,
  * compare, wall}.  Returns 0 or -errno.                                       */

@@ -47,6 +47,25 @@ def test_counters_equal_the_oracle(c5_file, opts):
         assert "nr_ram2gpu: 0, nr_ssd2gpu: 131072, average DMA blocks: 256.00" in r.stdout
 
 
+@pytest.mark.parametrize("members,stripe_kb", [(4, 128), (2, 1024), (8, 64)])
+def test_stripe_set_gives_the_flat_files_counters(c5_file, tmp_path, members, stripe_kb):
+    """-S: the same relation as the members of a stripe set (RAID-0 layout,
+    kmod/nvme_strom.c:736-820): identical counters, byte-compare clean, and with stripes of at
+    least 128 KB the same request accounting as the flat file"""
+    from nvme_strom_b200.loader import stripe_split
+    paths = [str(tmp_path / f"m{i}") for i in range(members)]
+    stripe_split(c5_file, paths, stripe_kb << 10)
+    for opts in (["-k"], ["-c"]):
+        r = subprocess.run([TOOL, "-d", "0", "-S", str(stripe_kb)] + opts + paths, capture_output=True, text=True,
+                           timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert parse_scan(r.stdout) == golden()
+        if "-c" in opts:
+            assert "verify: mismatch_blocks=0" in r.stdout
+        avg = 256.0 if stripe_kb >= 128 else stripe_kb * 2.0
+        assert f"nr_ram2gpu: 0, nr_ssd2gpu: 131072, average DMA blocks: {avg:.2f}" in r.stdout
+
+
 def test_mapping_dump_and_usage(c5_file):
     r = subprocess.run([TOOL, "-d", "0", "-p", c5_file], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "Mapped GPU Memory (handle: 0x" in r.stdout and "GPU Page: version=1, size=65536" in r.stdout
