@@ -9,7 +9,8 @@ copy switched off), the load+scan rate, per-GPU rates, and what the engine decid
   setting = readers:slot_kb:slots[:copy[:aff[:src]]]
      readers 0 = self-adjusting; slot_kb 0 = the engine's default for its cores
      copy = memcpy | nta | ntstore          aff = split (each rank keeps to its share of the cores) | none
-     src  = file (ext4 under dir, staged) | shm (tmpfs, page-locked: zero-copy)"""
+     src  = file (ext4 under dir, staged) | shm (tmpfs, page-locked: zero-copy)
+     further fields NAME=VALUE set other NVME_STROM_* knobs for that setting (NVME_STROM_SUB_KB=128 ...)"""
 import json
 import os
 import subprocess
@@ -42,6 +43,11 @@ for k, text in enumerate(settings):
     f = text.split(":")
     f += ["memcpy", "split", "file"][len(f) - 3:] if len(f) < 6 else []
     readers, slot_kb, slots, copy, aff, src = f[:6]
+    for name in ("NVME_STROM_SUB_KB", "NVME_STROM_SPIN_US", "NVME_STROM_ZC_PIECE_MB", "NVME_STROM_ADAPTIVE"):
+        os.environ.pop(name, None)
+    for extra in f[6:]:                                   # NAME=VALUE: any other NVME_STROM_* knob, this setting only
+        name, _, val = extra.partition("=")
+        os.environ[name] = val
     for name, val in (("NVME_STROM_READERS", readers), ("NVME_STROM_SLOT_KB", slot_kb)):
         if int(val) > 0: os.environ[name] = val
         else: os.environ.pop(name, None)
@@ -82,6 +88,7 @@ def main():
     shm_path = "/dev/shm/ring_sweep.heap"
     heapgen_file(path, 0x5EED0001, n * 131072)
     want_shm = any(s.split(":")[5:6] == ["shm"] for s in settings)
+    print("# " + " ".join(sys.argv), flush=True)
     if want_shm:
         heapgen_file(shm_path, 0x5EED0001, n * 131072)
     print(f"# {n} GPUs, {os.cpu_count()} cpus, file {path}", flush=True)
