@@ -267,6 +267,13 @@ int nvme_strom_unpin_file(int fdesc);
 int nvme_strom_stripe_open(const int *member_fds, unsigned int n_members, uint64_t stripe_bytes);
 int nvme_strom_stripe_close(int token);
 
+/* Is GPUDirect Storage in use?  Returns 1 when loads go SSD -> GPU through cuFile, 0 when they take
+ * the staged path (pinned host ring + cudaMemcpyAsync); `reason` (may be NULL) receives one line
+ * saying why: libcufile missing, nvidia-fs kernel module not loaded (cuFile's compatibility mode
+ * is a slower form of the staged path and does not count), or present-but-unused.  Looks only:
+ * never initialises the cuFile driver.  No reference counterpart (the module IS the direct path). */
+int nvme_strom_gds_status(char *reason, size_t len);
+
 /* The text the proc entry returns on read(2) (kmod/nvme_strom.c:2036-2061).
  * Copies at most len bytes, returns the number copied. */
 size_t nvme_strom_version(char *buf, size_t len);

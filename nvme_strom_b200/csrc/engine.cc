@@ -1099,6 +1099,7 @@ Engine *engine_for_window(const GpuWindow &w)
 	auto it = g_engines.find(key);
 	if (it != g_engines.end())
 		return it->second;
+	gds_log_once();
 	Engine *e = new Engine(w.device, w.ctx, false, config());
 	g_engines[key] = e;
 	return e;

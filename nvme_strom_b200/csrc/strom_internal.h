@@ -196,6 +196,7 @@ int stat_info_level();                    /* NVME_STROM_STAT_INFO, default 1    
 void stats_dma_started();
 void stats_dma_finished(uint64_t tsc_start);
 
+void gds_log_once();                    /* gds.cc: says once (NVME_STROM_VERBOSE=1) why GDS is off */
 int preload_kernels();                   /* page_scan.cu: load the default kernels now */
 
 /* driver-API entry points fetched through the runtime (no link to libcuda) */

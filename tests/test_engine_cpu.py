@@ -95,3 +95,25 @@ def test_dma_buffer_on_a_numa_node(strom):
     m[:] = b"\x5a" * arg.length                                 # every page can be allocated on the node
     assert m[arg.length - 1] == 0x5a
     m.close()
+
+
+def test_gds_probe_says_why_and_the_staged_path_is_what_runs(strom, tmp_path):
+    """north_star (2): cuFile only if the host exposes it.  This image has neither nvidia-fs nor a
+    cuFile data path in the library: the probe answers 0 with a reason, and a load goes through the
+    staged engine all the same (MEMCPY_SSD2RAM here; the GPU tests cover MEMCPY_SSD2GPU)."""
+    import ctypes as C
+    buf = C.create_string_buffer(256)
+    strom.lib.nvme_strom_gds_status.argtypes = [C.c_char_p, C.c_size_t]
+    assert strom.lib.nvme_strom_gds_status(buf, 256) == 0
+    text = buf.value.decode()
+    assert text.startswith("GDS ") and "staged path" in text
+    if not os.path.exists("/proc/driver/nvidia-fs/version"):
+        assert "nvidia-fs" in text or "libcufile" in text
+    assert strom.lib.nvme_strom_gds_status(None, 0) == 0
+    out = run_child("""
+        m, base = dmabuf(1 << 20)
+        assert wait(ssd2ram(fd, base, list(range(128)))) == (0, 0, 0)
+        assert m[:128 * 8192] == open(path, "rb").read()[:128 * 8192]
+        print("ok")
+    """, make_file(tmp_path, strom, 256), NVME_STROM_VERBOSE="1")
+    assert "ok" in out

@@ -44,6 +44,7 @@ def gpu_items(buf, first_blkno, max_items=None):
 
 
 @pytest.mark.parametrize("n_pages,first,mixed", [(1, 0, False), (7, 5, True), (300, 0xFFFFFF00, True),
+                                                 (511, 3, True), (512, 3, True), (513, 3, True), (1025, 9, True),
                                                  (9000, 100, True), (8192 * 3 + 17, 0, False)])
 def test_items_match_the_oracle(oracle, n_pages, first, mixed):
     buf = oracle.gen_pages(0x5EED0001, first, n_pages, mixed)

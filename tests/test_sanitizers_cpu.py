@@ -10,7 +10,7 @@ import pytest
 from conftest import ROOT
 
 CSRC = os.path.join(ROOT, "nvme_strom_b200", "csrc")
-HOST_SOURCES = ["common.cc", "heapgen.cc", "hostutil.cc", "registry.cc", "planner.cc", "stripe.cc", "engine.cc", "api.cc"]
+HOST_SOURCES = ["common.cc", "heapgen.cc", "hostutil.cc", "registry.cc", "planner.cc", "stripe.cc", "gds.cc", "engine.cc", "api.cc"]
 CUDA = os.environ.get("CUDA_HOME", "/usr/local/cuda")
 
 
