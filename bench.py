@@ -183,7 +183,7 @@ def run_product(args):
     import torch
     import torch.distributed as dist
 
-    from nvme_strom_b200 import abi, multigpu
+    from nvme_strom_b200 import abi, calibrate, multigpu
     from nvme_strom_b200.abi import lib
     from nvme_strom_b200.loader import SegmentPipeline, heapgen_file
 
@@ -291,49 +291,17 @@ def run_product(args):
         e2e = world * GIB / (ms_e2e * 1e-3) / 1e9
 
         # ---- transfer roofline, calibrated in the same run: min(H2D link, page-cache read rate) ----
-        def gather(x):
-            if world == 1:
-                return [x]
-            t = torch.tensor([x], dtype=torch.float64, device=dev)
-            out = [torch.empty_like(t) for _ in range(world)]
-            dist.all_gather(out, t)
-            return [float(o.item()) for o in out]
-
         # (a) the link: 512 MiB pinned -> device per rank, all ranks at once.  A trial's aggregate is
         # all bytes over the slowest rank's time; the best trial counts (not a sum of per-rank bests,
         # which no single moment ever saw)
-        host = torch.empty(GIB // 2, dtype=torch.uint8).pin_memory()
-        h2d_cal, h2d_per_rank = 0.0, []
-        for _ in range(8):
-            barrier()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            resident[:GIB // 2].copy_(host, non_blocking=True)
-            b.record()
-            torch.cuda.synchronize()
-            times = gather(a.elapsed_time(b) * 1e-3)
-            agg = world * (GIB // 2) / max(times) / 1e9
-            if agg > h2d_cal:
-                h2d_cal, h2d_per_rank = agg, [round((GIB // 2) / t / 1e9, 2) for t in times]
-        del host
+        h2d_cal, h2d_per_rank = calibrate.h2d_aggregate(dev, resident, GIB // 2, 8)
         h2d_total = h2d_cal
 
         # (b) the source: page-cache read rate of the same file range, by the same number of threads
         # an engine may use, into cache-resident scratch -- no staging ring, no device, so it does
         # not move with the staging geometry (all ranks at once, best of 3 passes)
         est = abi.engine_state(local_rank)
-        fd_src = os.open(path, os.O_RDONLY)
-        pc_best = 0.0
-        try:
-            for _ in range(3):
-                barrier()
-                t0 = time.perf_counter()
-                abi.pagecache_read_GBps(fd_src, first_page * 8192, shard_bytes, est["readers_max"])
-                times = gather(time.perf_counter() - t0)
-                pc_best = max(pc_best, world * shard_bytes / max(times) / 1e9)
-        finally:
-            os.close(fd_src)
-        source_total = pc_best
+        source_total = calibrate.pagecache_aggregate(dev, path, first_page * 8192, shard_bytes, est["readers_max"], 3)
 
         # (c) diagnosis only: the MEMCPY_SSD2GPU pipeline with the device copy switched off (moves
         # with the ring geometry; it is the pipeline's own source side, not a roofline)
@@ -495,7 +463,7 @@ def run_product(args):
             "data": "synthetic",
             "config": {"workload": "C2: 1 GiB synthetic PG heap file per GPU (131072 x 8KB pages, seed 0x5EED0001), "
                                    "32 MB segments x 6 slots, checksum + header + line-pointer scan",
-                       "file_dir": d, "page_cache": "warm", "l2": "input (1 GiB) >> L2 (126 MB), no flush needed",
+                       "file_dir": d, "file_system": calibrate.filesystem_of(d)[1], "page_cache": "warm", "l2": "input (1 GiB) >> L2 (126 MB), no flush needed",
                        "parallelism": f"{world} x independent shard, counters merged once",
                        "readers": os.environ.get("NVME_STROM_READERS", "self-adjusting"),
                        "cpus_per_rank": len(cpus_mine)},

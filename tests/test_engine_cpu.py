@@ -117,3 +117,28 @@ def test_gds_probe_says_why_and_the_staged_path_is_what_runs(strom, tmp_path):
         print("ok")
     """, make_file(tmp_path, strom, 256), NVME_STROM_VERBOSE="1")
     assert "ok" in out
+
+
+def test_rank_cpu_shares():
+    """one rank per GPU: ranks whose GPUs report the same neighbourhood split it evenly in rank order;
+    the shares are disjoint and cover the cores (utils/ssd2ram_test.c:66-119 is the precedent)"""
+    from nvme_strom_b200 import multigpu
+    none8 = [None] * 8
+    shares = [multigpu.rank_cpus(r, 8, allowed=range(32), local_lists=none8) for r in range(8)]
+    assert all(len(s) == 4 for s in shares) and sorted(sum(shares, [])) == list(range(32))
+    two_nodes = [list(range(0, 16))] * 4 + [list(range(16, 32))] * 4
+    shares = [multigpu.rank_cpus(r, 8, allowed=range(32), local_lists=two_nodes) for r in range(8)]
+    assert shares[0] == [0, 1, 2, 3] and shares[4] == [16, 17, 18, 19] and shares[7] == [28, 29, 30, 31]
+    # a job confined to some cores keeps to them; uneven splits lose nothing
+    shares = [multigpu.rank_cpus(r, 3, allowed=[2, 3, 5, 7, 11, 13, 17], local_lists=[None] * 3) for r in range(3)]
+    assert sorted(sum(shares, [])) == [2, 3, 5, 7, 11, 13, 17] and all(shares)
+    assert multigpu.rank_cpus(0, 1, allowed=range(6)) == list(range(6))
+    assert multigpu.rank_cpus(3, 4, allowed=[0, 1], local_lists=[None] * 4) == [0, 1]     # fewer cores than ranks
+    assert multigpu.parse_cpu_list("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11]
+
+
+def test_filesystem_lookup(tmp_path):
+    from nvme_strom_b200 import calibrate
+    mnt, fstype = calibrate.filesystem_of("/dev/shm")
+    assert fstype in ("tmpfs", "?") and mnt.startswith("/")
+    assert calibrate.filesystem_of(str(tmp_path))[1] != ""

@@ -3,7 +3,9 @@ prints one JSON object per config (rank 0).  Launch plain for 1 GPU or under tor
   C3  N x 8 GiB heap file sharded over N GPUs, segment size sweep 4 / 32 / 128 MB
   C4  MEMCPY_SSD2RAM (+H2D) vs MEMCPY_SSD2GPU, 16 GiB, 1 GPU
   C5  mixed-validity file, N x 1 GiB: merged counters must equal tests/golden/c5_expected_totals.json
-Sizes can be scaled with --c3-gib / --c4-gib (what was run is printed, never silently shrunk)."""
+Sizes can be scaled with --c3-gib / --c4-gib (what was run is printed, never silently shrunk).
+Every row carries the file system, the box's H2D and page-cache read rates calibrated in the same
+run (nvme_strom_b200/calibrate.py) and the row's fraction of each."""
 import argparse
 import json
 import os
@@ -15,7 +17,7 @@ sys.path.insert(0, ROOT)
 import torch
 import torch.distributed as dist
 
-from nvme_strom_b200 import abi, multigpu
+from nvme_strom_b200 import abi, calibrate, multigpu
 from nvme_strom_b200.loader import SegmentPipeline, heapgen_file
 
 GIB = 1 << 30
@@ -33,8 +35,27 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ.setdefault("NVME_STROM_READERS", str(max(4, min(16, (os.cpu_count() or 16) // world))))
+        # each rank keeps to its share of the cores; the engine sizes itself by what it is allowed on
+        os.sched_setaffinity(0, multigpu.rank_cpus(local, int(os.environ.get("LOCAL_WORLD_SIZE", world))))
         dist.init_process_group("nccl", device_id=dev)
+    fs = calibrate.filesystem_of(args.dir)[1]
+    cal = {}
+
+    def calibrated(path, offset, length):
+        """H2D and page-cache read rates of this box, once per run (the first file serves)"""
+        if not cal:
+            scratch = torch.empty(1 << 29, dtype=torch.uint8, device=dev)
+            cal["h2d_GBps"], cal["h2d_per_rank_GBps"] = calibrate.h2d_aggregate(dev, scratch, 1 << 29, 6)
+            del scratch
+            threads = abi.engine_state(local)["readers_max"]
+            cal["page_cache_read_GBps"] = calibrate.pagecache_aggregate(dev, path, offset, min(length, 4 * GIB), threads, 2)
+        return cal
+
+    def fractions(gbps, c, zero_copy=False):
+        roof = c["h2d_GBps"] if zero_copy else min(c["h2d_GBps"], c["page_cache_read_GBps"])
+        return {"file_system": fs, "h2d_GBps": round(c["h2d_GBps"], 1),
+                "page_cache_read_GBps": round(c["page_cache_read_GBps"], 1),
+                "frac_of_h2d": round(gbps / c["h2d_GBps"], 3), "frac_of_transfer_roofline": round(gbps / roof, 3)}
 
     def barrier():
         if world > 1:
@@ -82,9 +103,11 @@ def main():
         merged = multigpu.reduce_totals(tot, dev)
         gold = json.load(open(os.path.join(ROOT, "tests", "golden", "c5_expected_totals.json")))["totals_by_gib"]
         want = gold.get(str(world))
-        res = {"config": "C5 mixed-validity", "n_gpus": world, "file_gib": world, "GBps": round(world * GIB / dt / 1e9, 2),
+        c = calibrated(path, first * seg, n * seg)
+        gbps = world * GIB / dt / 1e9
+        res = {"config": "C5 mixed-validity", "n_gpus": world, "file_gib": world, "GBps": round(gbps, 2),
                "totals": merged[:13], "expected": want[:13] if want else None,
-               "bit_exact": (merged == want) if want else None}
+               "bit_exact": (merged == want) if want else None, **fractions(gbps, c, args.pin)}
         out.append(res)
         barrier()
         if rank == 0:
@@ -101,8 +124,11 @@ def main():
             merged = multigpu.reduce_totals(tot, dev)
             ok = merged[abi.T_PAGES] == world * args.c3_gib * GIB // 8192 and merged[abi.T_CHECKSUM_FAIL] == 0 \
                 and merged[abi.T_INVALID] == 0
+            c = calibrated(path, first * seg, n * seg)
+            gbps = world * args.c3_gib * GIB / dt / 1e9
             out.append({"config": "C3 sharded load+scan", "n_gpus": world, "file_gib": world * args.c3_gib,
-                        "segment_mb": seg_mb, "GBps": round(world * args.c3_gib * GIB / dt / 1e9, 2),
+                        "segment_mb": seg_mb, "GBps": round(gbps, 2), **fractions(gbps, c, args.pin),
+                        "engine": abi.engine_state(local),
                         "GBps_per_gpu": round(args.c3_gib * GIB / dt / 1e9, 2), "clean_file_no_failures": ok,
                         "page_cache": "bypassed (O_DIRECT)" if os.environ.get("NVME_STROM_IO") == "direct" else ("warm, page-locked (zero-copy)" if args.pin else "warm")})
         barrier()
@@ -119,6 +145,7 @@ def main():
             tot, cnt, dt = timed_run(pipe, path, 0, n, reps=1)
             pipe.close()
             res[name + "_GBps"] = round(args.c4_gib * GIB / dt / 1e9, 2)
+            res[name + "_fractions"] = fractions(args.c4_gib * GIB / dt / 1e9, calibrated(path, 0, n * seg))
             res[name + "_pages"] = tot[abi.T_PAGES]
             res[name + "_xor"] = tot[abi.T_XOR_CHECKSUM]
         res["same_result"] = res["ssd2gpu_xor"] == res["ssd2ram_then_h2d_xor"] and res["ssd2gpu_pages"] == res["ssd2ram_then_h2d_pages"]
