@@ -254,16 +254,9 @@ class SegmentPipeline:
 def heapgen_file(path, seed, n_pages, mixed=False, n_threads=None, first_page=0):
     """Writes the SURVEY 8d synthetic heap file with the library's generator."""
     if n_threads is None:
-        n_threads = min(os.cpu_count() or 1, 32)
+        n_threads = min(len(os.sched_getaffinity(0)) or 1, 32)      # the cores this process may use
     abi.check(lib.strom_heapgen_file(path.encode(), seed, first_page, n_pages, int(mixed), n_threads),
               "strom_heapgen_file")
-
-
-def partition_segments(n_segments, n_parts, rank):
-    first, count = C.c_uint64(), C.c_uint64()
-    abi.check(lib.strom_partition_segments(n_segments, n_parts, rank, C.byref(first), C.byref(count)),
-              "strom_partition_segments")
-    return first.value, count.value
 
 
 def stripe_split(src_path, member_paths, stripe_bytes):
