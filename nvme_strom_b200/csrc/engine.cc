@@ -1191,8 +1191,18 @@ extern "C" int strom_debug_reconfigure(void)
 {
 	using namespace strom;
 	std::lock_guard<std::mutex> g(g_engine_lock);
-	for (auto &kv : g_engines)
-		if (!kv.second->idle()) { errno = EBUSY; return -1; }
+	/* a task's waiter is released a moment before the reader that retired its last slot marks the
+	 * slot free: give that moment (and no more than a second) before calling the engine busy */
+	for (int tries = 0;; tries++)
+	{
+		bool busy = false;
+		for (auto &kv : g_engines)
+			busy = busy || !kv.second->idle();
+		if (!busy)
+			break;
+		if (tries >= 1000) { errno = EBUSY; return -1; }
+		usleep(1000);
+	}
 	for (auto &kv : g_engines)
 		delete kv.second;
 	g_engines.clear();

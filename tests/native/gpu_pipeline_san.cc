@@ -198,8 +198,8 @@ int main(int argc, char **argv)
 			cp.chunk_sz = 8192;
 			cp.chunk_ids = ids.data();
 			CHECK(nvme_strom_ioctl(STROM_IOCTL__MEMCPY_SSD2GPU, &cp) == 0);
-			int busy = strom_debug_reconfigure();                     /* most likely still in flight */
-			CHECK(busy == 0 || errno == EBUSY);
+			/* (reconfigure waits up to a second for the engines to fall idle, so it is not called
+			 * with a task in flight here: that would only test the clock) */
 			StromCmd__MemCopyWait wt;
 			memset(&wt, 0, sizeof(wt));
 			wt.dma_task_id = cp.dma_task_id;

@@ -35,15 +35,18 @@ pipe = SegmentPipeline(rank, 32 << 20, 6)
 n_seg = 32
 def barrier(name):
     open("%%s.b.%%s.%%d" %% (path, name, rank), "w").close()
+    deadline = time.time() + 60
     for r in range(world):
         while not os.path.exists("%%s.b.%%s.%%d" %% (path, name, r)):
+            if time.time() > deadline:
+                sys.exit("rank %%d: rank %%d never reached barrier %%s" %% (rank, r, name))
             time.sleep(0.0005)
 pinned = False
 for k, text in enumerate(settings):
     f = text.split(":")
     f += ["memcpy", "split", "file"][len(f) - 3:] if len(f) < 6 else []
     readers, slot_kb, slots, copy, aff, src = f[:6]
-    for name in ("NVME_STROM_SUB_KB", "NVME_STROM_SPIN_US", "NVME_STROM_ZC_PIECE_MB", "NVME_STROM_ADAPTIVE"):
+    for name in ("NVME_STROM_SUB_KB", "NVME_STROM_SPIN_US", "NVME_STROM_ZC_PIECE_MB", "NVME_STROM_ADAPTIVE", "NVME_STROM_WC"):
         os.environ.pop(name, None)
     for extra in f[6:]:                                   # NAME=VALUE: any other NVME_STROM_* knob, this setting only
         name, _, val = extra.partition("=")
@@ -98,7 +101,7 @@ def main():
         rows = {}
         for p in procs:
             try:
-                o, _ = p.communicate(timeout=180 + 40 * len(settings))
+                o, _ = p.communicate(timeout=90 + 12 * len(settings))
             except Exception:                                # noqa: BLE001
                 p.kill()
                 o = ""
