@@ -431,6 +431,30 @@ def run_product(args):
                 torch.cuda.synchronize()
                 extras[name] = round(nbytes / (a.elapsed_time(b) / args.steps * 1e-3) / 1e9, 1)
             del ref
+            # the step after the path: LP_NORMAL items of the resident shard as a packed array
+            n_items_cap = pages_mine * 220
+            items = torch.empty(n_items_cap * 3, dtype=torch.int32, device=dev)
+            offs = torch.empty(pages_mine + 1, dtype=torch.int64, device=dev)
+            n_items = torch.zeros(1, dtype=torch.int64, device=dev)
+            ext = lambda: abi.check(lib.strom_extract_items_dev(p_res, pages_mine, first_page & 0xFFFFFFFF,
+                                                                C.c_void_p(items.data_ptr()), n_items_cap,
+                                                                C.c_void_p(offs.data_ptr()), C.c_void_p(n_items.data_ptr()), st),
+                                    "strom_extract_items_dev")
+            with torch.cuda.stream(stream):
+                for _ in range(3):
+                    ext()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream)
+                for _ in range(args.steps):
+                    ext()
+                b.record(stream)
+            torch.cuda.synchronize()
+            ext_ms = a.elapsed_time(b) / args.steps
+            extras["extract_items"] = {"ms_per_GiB_of_pages": round(ext_ms, 3), "items": int(n_items.item()),
+                                       "Mitems_per_s": round(int(n_items.item()) / ext_ms / 1e3, 1),
+                                       "launches": 3, "note": "count + tile scan + emit (extract.cu); reads the line-pointer "
+                                                              "arrays twice, ~0.5 KB of each page, latency- not HBM-bound"}
+            del items, offs
             vp = SegmentPipeline(local_rank, SEG, SLOTS, verify=True)
             vp.run(path, first_seg, n_seg)
             t0 = time.perf_counter()

@@ -39,6 +39,17 @@ def _rank_main(rank, world, port, path, seg_pages, out_path):
                        count=count * seg_pages * 8192)
     _, tot = oracle.scan(data, first * seg_pages)
     merged = multigpu.reduce_totals(tot, device="cpu")
+    # every rank keeps to its share of the cores, and an engine made afterwards counts that share
+    # (what bench.py does before its first MAP_GPU_MEMORY); the shares of all ranks are disjoint
+    from nvme_strom_b200 import abi
+    everyone = sorted(os.sched_getaffinity(0))
+    mine = multigpu.rank_cpus(rank, world, allowed=everyone, local_lists=[None] * world)
+    os.sched_setaffinity(0, mine)
+    seen = torch.zeros(max(everyone) + 1, dtype=torch.int64)
+    seen[mine] = 1
+    dist.all_reduce(seen)
+    assert int(seen.max()) == 1 or len(everyone) < world
+    assert abi.engine_state(0)["allowed_cpus"] == len(mine)
     if rank == 0:
         np.save(out_path, np.array(merged, dtype=np.uint64))
     dist.destroy_process_group()
