@@ -714,6 +714,7 @@ private:
 		uint32_t unfilled = 0;            /* sub-pieces handed out or still to hand out    */
 		long status = 0;                  /* first error among the fillers                 */
 		bool backlog = false;             /* more pieces were waiting when this one was taken */
+		bool after_pause = false;         /* the ring was idle when this one was taken     */
 	};
 
 	void retire_stage(Stage &st)
@@ -767,62 +768,96 @@ private:
 
 	/*
 	 * How many readers take part (lock held).  Evidence is gathered over windows of 64 staged
-	 * slots: a slot counts as starved when it was queued behind a finished copy although more
+	 * slots.  A slot counts as starved when it was queued behind a finished copy although more
 	 * pieces were waiting -- the readers, not the link, set the pace.  Measured on B200 (profiles/
-	 * r02_ring_n1.txt): at the link-bound reader count about 0.3 % of the slots are starved, one
-	 * reader short of it 5 %, two short 40 %.  So: two or more starved slots in a window (3 %) let
-	 * one more reader in -- two more when a quarter of the window starved; eight windows in a row
-	 * without any let one go.  When letting one go is answered by starvation within two windows,
-	 * the count goes back up and stays put for a while that doubles every time (the link-bound
-	 * point has been found; there is no reason to keep probing it).
+	 * r02_ring_n1_first_controller.txt): at the link-bound reader count about 0.3 % of the slots
+	 * are starved, one reader short of it 5 %, two short 40 %; past it every extra reader costs
+	 * throughput (12 instead of 6: -10 %).  Starvation alone is not a reason to add readers,
+	 * though: when something else holds the readers back (the host's memory system with eight
+	 * GPUs loading at once, a second engine competing for the cores), more of them only make it
+	 * worse.  So every change is a trial judged by the window that follows it:
+	 *   - two or more starved slots in a window (3 %): one more reader, kept only if the next
+	 *     window moved at least 3 % more bytes per second; otherwise taken back, and no further
+	 *     growth is tried for a while that doubles with every failed trial;
+	 *   - eight windows in a row without a starved slot: one reader fewer, kept unless the next
+	 *     window lost more than 2 %; a failed trial again doubles the wait before the next.
+	 * Windows that contain a pause (the caller had nothing queued) say nothing and are skipped.
 	 */
-	void account_slot(bool starved)
+	static double now_s()
+	{
+		struct timespec ts;
+		clock_gettime(CLOCK_MONOTONIC, &ts);
+		return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+	}
+	void account_slot(bool starved, bool after_pause, uint32_t bytes)
 	{
 		n_issued_++;
 		if (starved)
 			n_starved_++;
 		if (!cfg_->adaptive)
 			return;
+		if (after_pause || win_issued_ == 0)
+		{
+			if (after_pause)
+				win_paused_ = win_issued_ > 0;        /* a pause inside a window spoils its rate */
+			if (win_issued_ == 0)
+				win_t0_ = now_s();
+		}
 		win_issued_++;
+		win_bytes_ += bytes;
 		if (starved)
 			win_starved_++;
 		if (win_issued_ < 64)
 			return;
+		const double t1 = now_s();
+		const double rate = t1 > win_t0_ ? (double)win_bytes_ / (t1 - win_t0_) : 0;
+		const bool valid = !win_paused_ && rate > 0;
 		const int max = (int)threads_.size();
-		if (win_starved_ >= 2)
+		if (trial_ != 0 && valid)
 		{
-			const int step = win_starved_ * 4 >= win_issued_ ? 2 : 1;
-			const int to = std::min(max, active_ + step);
-			if (to > active_)
+			/* judge the change made at the end of the previous window */
+			const bool keep = trial_ > 0 ? rate >= trial_base_ * 1.03 : rate >= trial_base_ * 0.98;
+			if (!keep)
 			{
-				n_grown_ += (uint64_t)(to - active_);
-				active_ = to;
+				active_ -= trial_;                    /* take it back */
+				if (trial_ > 0) { n_shrunk_++; grow_hold_ = grow_hold_next_; grow_hold_next_ = std::min<uint32_t>(grow_hold_next_ * 2, 4096); }
+				else { n_grown_++; park_cv_.notify_all(); shrink_hold_ = shrink_hold_next_; shrink_hold_next_ = std::min<uint32_t>(shrink_hold_next_ * 2, 4096); }
+			}
+			else if (trial_ > 0)
+				grow_hold_next_ = 8;                  /* growth paid off: keep probing readily */
+			trial_ = 0;
+			calm_ = 0;
+		}
+		else if (trial_ == 0 && valid)
+		{
+			if (grow_hold_ > 0) grow_hold_--;
+			if (shrink_hold_ > 0) shrink_hold_--;
+			if (win_starved_ >= 2 && active_ < max && grow_hold_ == 0)
+			{
+				trial_base_ = rate;
+				trial_ = +1;
+				active_++;
+				n_grown_++;
 				park_cv_.notify_all();
-			}
-			if (since_shrink_ <= 2)                   /* that reader was needed */
-			{
-				hold_ = hold_next_;
-				hold_next_ = std::min<uint32_t>(hold_next_ * 2, 4096);
-			}
-			calm_ = 0;
-		}
-		else if (win_starved_ == 0)
-		{
-			if (hold_ > 0)
-				hold_--;
-			else if (++calm_ >= 8 && active_ > 2)
-			{
-				active_--;
-				n_shrunk_++;
 				calm_ = 0;
-				since_shrink_ = 0;
 			}
+			else if (win_starved_ == 0 && active_ > 2)
+			{
+				if (++calm_ >= 8 && shrink_hold_ == 0)
+				{
+					trial_base_ = rate;
+					trial_ = -1;
+					active_--;
+					n_shrunk_++;
+					calm_ = 0;
+				}
+			}
+			else
+				calm_ = 0;
 		}
-		else
-			calm_ = 0;
-		if (since_shrink_ < 1000)
-			since_shrink_++;
 		win_issued_ = win_starved_ = 0;
+		win_bytes_ = 0;
+		win_paused_ = false;
 	}
 
 	/* A reader that has to wait for a slot waits for a copy to finish, some tens of
@@ -935,7 +970,7 @@ private:
 					{
 						o.task = o.piece.task;
 						o.tsc = t0;
-						account_slot(link_idle && o.backlog);
+						account_slot(link_idle && o.backlog, o.after_pause, o.piece.length);
 					}
 					o.state = in_flight ? kInFlight : kFree;
 					announce_change();
@@ -973,6 +1008,7 @@ private:
 				for (const Stage &other : stages_)
 					ring_busy = ring_busy || (&other != &n && other.state != kFree);
 				n.backlog = !queue_.empty() && (ring_busy || was_in_flight);
+				n.after_pause = !(ring_busy || was_in_flight);
 				n.state = kPreparing;
 				open_ = idx;
 				g.unlock();
@@ -1079,7 +1115,12 @@ private:
 	std::condition_variable cv_;
 	std::condition_variable park_cv_;     /* readers beyond active_ wait here      */
 	int active_ = 1;                      /* readers taking part                   */
-	uint32_t win_issued_ = 0, win_starved_ = 0, calm_ = 0, hold_ = 0, hold_next_ = 32, since_shrink_ = 1000;
+	uint32_t win_issued_ = 0, win_starved_ = 0, calm_ = 0;
+	uint32_t grow_hold_ = 0, grow_hold_next_ = 8, shrink_hold_ = 0, shrink_hold_next_ = 32;
+	uint64_t win_bytes_ = 0;
+	double win_t0_ = 0, trial_base_ = 0;
+	bool win_paused_ = false;
+	int trial_ = 0;                       /* +1 / -1: the change under trial, 0: none      */
 	uint64_t n_grown_ = 0, n_shrunk_ = 0, n_starved_ = 0, n_issued_ = 0;
 	std::deque<Job> queue_;
 	std::condition_variable ready_cv_;
