@@ -62,6 +62,14 @@ int strom_debug_skip_h2d(int on);
  * file cannot be mapped / NVME_STROM_SRC=pread; EIO: a read faulted). */
 int strom_debug_pagecache_read(int fdesc, uint64_t offset, uint64_t length, int n_threads, double *seconds);
 
+/* The same readers copying into a destination of dest_bytes_per_thread each that they walk round
+ * and round (16 MB: it does not stay in a core's cache): the host's plain copy rate out of the page
+ * cache.  A staged path -- file -> pinned buffer -> DMA -- cannot move more than this, and moves
+ * less once the DMA engines read the buffers as well; reported beside the transfer roofline as
+ * the staged path's ceiling on the box at hand. */
+int strom_debug_host_copy(int fdesc, uint64_t offset, uint64_t length, int n_threads,
+						  uint64_t dest_bytes_per_thread, double *seconds);
+
 /* Tuning tools only: tears the idle engines down and re-reads the NVME_STROM_* environment, so that
  * one process can sweep staging geometries.  -1/EBUSY while a transfer is in flight.  Windows stay
  * mapped; the next MEMCPY_* call builds new engines. */

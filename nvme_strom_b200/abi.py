@@ -127,6 +127,7 @@ lib.nvme_strom_stripe_close.argtypes = [C.c_int]
 lib.strom_stripe_map_debug.argtypes = [C.POINTER(C.c_uint64), C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32,
                                        C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
 lib.strom_debug_pagecache_read.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
+lib.strom_debug_host_copy.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.c_uint64, C.POINTER(C.c_double)]
 
 
 class StromEngineState(C.Structure):
@@ -150,10 +151,15 @@ def engine_state(device):
     return st.as_dict()
 
 
-def pagecache_read_GBps(fd, offset, length, n_threads=0):
-    """page-cache read rate of a file range (strom_debug.h), GB/s"""
+def pagecache_read_GBps(fd, offset, length, n_threads=0, dest_bytes_per_thread=0):
+    """page-cache read rate of a file range (strom_debug.h), GB/s; with dest_bytes_per_thread > 0 the
+    host's plain copy rate into per-thread buffers of that size (strom_debug_host_copy)"""
     secs = C.c_double()
-    check(lib.strom_debug_pagecache_read(fd, offset, length, n_threads, C.byref(secs)), "strom_debug_pagecache_read")
+    if dest_bytes_per_thread:
+        check(lib.strom_debug_host_copy(fd, offset, length, n_threads, dest_bytes_per_thread, C.byref(secs)),
+              "strom_debug_host_copy")
+    else:
+        check(lib.strom_debug_pagecache_read(fd, offset, length, n_threads, C.byref(secs)), "strom_debug_pagecache_read")
     return length / secs.value / 1e9
 lib.nvme_strom_version.argtypes = [C.c_char_p, C.c_size_t]
 lib.nvme_strom_version.restype = C.c_size_t

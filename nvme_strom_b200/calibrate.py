@@ -50,10 +50,12 @@ def h2d_aggregate(dev, dst, nbytes=1 << 29, trials=8):
     return best, per_rank
 
 
-def pagecache_aggregate(dev, path, offset, length, n_threads, passes=3):
+def pagecache_aggregate(dev, path, offset, length, n_threads, passes=3, dest_bytes_per_thread=0):
     """Page-cache read rate of this rank's range of `path`, every rank at once, by `n_threads`
     readers per rank copying into cache-resident scratch (strom_debug_pagecache_read: no staging
-    ring, no device).  All bytes over the slowest rank's time, best pass.  GB/s."""
+    ring, no device).  All bytes over the slowest rank's time, best pass.  GB/s.
+    dest_bytes_per_thread > 0: the host's plain copy rate instead (every reader walks a destination
+    of that size, which does not stay in cache) -- the ceiling of any staged path on this host."""
     world = dist.get_world_size() if dist.is_initialized() else 1
     fd = os.open(path, os.O_RDONLY)
     best = 0.0
@@ -61,7 +63,7 @@ def pagecache_aggregate(dev, path, offset, length, n_threads, passes=3):
         for _ in range(passes):
             _barrier()
             t0 = time.perf_counter()
-            abi.pagecache_read_GBps(fd, offset, length, n_threads)
+            abi.pagecache_read_GBps(fd, offset, length, n_threads, dest_bytes_per_thread)
             times = gather_floats(time.perf_counter() - t0, dev)
             best = max(best, world * length / max(times) / 1e9)
     finally:

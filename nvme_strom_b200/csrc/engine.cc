@@ -1164,7 +1164,8 @@ void engine_submit(Engine *e, const std::vector<Job> &jobs) { e->submit(jobs); }
  * transfer roofline (north_star: the slower of page-cache read bandwidth and PCIe H2D); it does
  * not move with the staging geometry.
  */
-static int pagecache_read_rate(int fd, uint64_t offset, uint64_t length, int n_threads, double *seconds)
+static int pagecache_read_rate(int fd, uint64_t offset, uint64_t length, int n_threads, uint64_t scratch_bytes,
+							   double *seconds)
 {
 	struct stat st;
 	if (fstat(fd, &st) != 0)
@@ -1179,6 +1180,9 @@ static int pagecache_read_rate(int fd, uint64_t offset, uint64_t length, int n_t
 	if (n_threads <= 0)
 		n_threads = cfg->readers_max;
 	const uint32_t sub = cfg->sub_bytes;
+	/* scratch_bytes > sub: every reader walks a destination of that size instead (a ring that does
+	 * NOT stay in its cache) -- the plain copy rate of the host, the ceiling of any staged path */
+	const uint64_t scratch_sz = std::max<uint64_t>(sub, scratch_bytes / sub * sub);
 	std::atomic<uint64_t> cursor{0};
 	std::atomic<int> failed{0}, ready{0};
 	std::atomic<bool> go{false};
@@ -1188,8 +1192,9 @@ static int pagecache_read_rate(int fd, uint64_t offset, uint64_t length, int n_t
 			if (cfg->pin)
 				(void)sched_setaffinity(0, sizeof(cfg->cpus), &cfg->cpus);
 			void *scratch = nullptr;
-			if (posix_memalign(&scratch, 4096, sub) != 0) { failed++; ready++; return; }
-			memset(scratch, 0, sub);
+			if (posix_memalign(&scratch, 4096, scratch_sz) != 0) { failed++; ready++; return; }
+			memset(scratch, 0, scratch_sz);
+			uint64_t at_dst = 0;
 			ready++;
 			while (!go.load(std::memory_order_acquire))
 				sched_yield();
@@ -1199,8 +1204,9 @@ static int pagecache_read_rate(int fd, uint64_t offset, uint64_t length, int n_t
 				if (at >= length)
 					break;
 				const uint32_t n = (uint32_t)std::min<uint64_t>(sub, length - at);
-				if (copy_from_map(*m, (char *)scratch, n, offset + at, 0) != 0)
+				if (copy_from_map(*m, (char *)scratch + at_dst, n, offset + at, 0) != 0)
 					failed++;
+				at_dst = (at_dst + sub) % scratch_sz;
 			}
 			free(scratch);
 		});
@@ -1223,7 +1229,16 @@ extern "C" int strom_debug_skip_h2d(int on) { return strom::g_skip_h2d.exchange(
 extern "C" int strom_debug_pagecache_read(int fdesc, uint64_t offset, uint64_t length, int n_threads, double *seconds)
 {
 	if (!seconds) { errno = EINVAL; return -1; }
-	int rc = strom::pagecache_read_rate(fdesc, offset, length, n_threads, seconds);
+	int rc = strom::pagecache_read_rate(fdesc, offset, length, n_threads, 0, seconds);
+	if (rc != 0) { errno = -rc; return -1; }
+	return 0;
+}
+
+extern "C" int strom_debug_host_copy(int fdesc, uint64_t offset, uint64_t length, int n_threads,
+									 uint64_t dest_bytes_per_thread, double *seconds)
+{
+	if (!seconds) { errno = EINVAL; return -1; }
+	int rc = strom::pagecache_read_rate(fdesc, offset, length, n_threads, dest_bytes_per_thread, seconds);
 	if (rc != 0) { errno = -rc; return -1; }
 	return 0;
 }

@@ -77,6 +77,7 @@ def test_pagecache_read_calibration(tmp_path, strom):
         for threads in (1, 3, 0):
             assert strom.pagecache_read_GBps(fd, 0, 64 << 20, threads) > 0.05
         assert strom.pagecache_read_GBps(fd, 32 << 20, 1 << 40, 2) > 0       # clipped to the file
+        assert strom.pagecache_read_GBps(fd, 0, 64 << 20, 2, dest_bytes_per_thread=16 << 20) > 0.05   # plain copy
         assert strom.lib.nvme_strom_unpin_file(fd) == 0
         assert strom.pagecache_read_GBps(fd, 0, 64 << 20, 2) > 0             # mapped again on demand
     finally:

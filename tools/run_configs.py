@@ -37,6 +37,7 @@ def main():
     if world > 1:
         # each rank keeps to its share of the cores; the engine sizes itself by what it is allowed on
         os.sched_setaffinity(0, multigpu.rank_cpus(local, int(os.environ.get("LOCAL_WORLD_SIZE", world))))
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")    # keep stdout to the JSON lines
         dist.init_process_group("nccl", device_id=dev)
     fs = calibrate.filesystem_of(args.dir)[1]
     cal = {}
