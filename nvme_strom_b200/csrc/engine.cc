@@ -43,7 +43,7 @@
  * pins an engine's readers to an explicit set instead.
  *
  * Environment: NVME_STROM_READERS (fixed reader count per engine; unset: self-
- * adjusting between 2 and 3/4 of the allowed cores, at most 16),
+ * adjusting between 2 and all allowed cores but one, at most 16),
  * NVME_STROM_SLOT_KB (staging slot; unset: 4096, or 512 per allowed core below
  * 8 cores), NVME_STROM_SLOTS (ring length, default 4), NVME_STROM_SUB_KB (what
  * one reader copies at a time, default 256), NVME_STROM_SPIN_US (yield-spin
@@ -146,10 +146,12 @@ static EngineConfig load_config()
 	c.slot_bytes = (uint32_t)env_int("NVME_STROM_SLOT_KB", slot_kb_dflt, 128, 65536) << 10;
 	c.slots = env_int("NVME_STROM_SLOTS", 4, 2, 64);
 	c.sub_bytes = (uint32_t)env_int("NVME_STROM_SUB_KB", 256, 64, 65536) << 10;
-	/* readers: a lone GPU is link-bound from about 6 on; the rest of the cores is needed by the
-	 * caller, the driver's threads and the SSD2RAM engine.  Up to 4 cores every core reads (the
-	 * caller sleeps in MEMCPY_WAIT meanwhile). */
-	c.readers_max = c.ncpu <= 4 ? std::max(2, c.ncpu) : std::min(16, c.ncpu * 3 / 4);
+	/* readers: a lone GPU is link-bound from about 6 on, so that is where an engine starts; how many
+	 * of its threads take part after that is decided by trial (Engine::account_slot), up to all
+	 * cores but one (the caller's; up to 4 cores every core reads -- the caller sleeps in
+	 * MEMCPY_WAIT meanwhile).  Four ranks of eight cores each on one host want 7 (profiles/
+	 * r02_bench_n4*.json: at 6 of 6 readers 60 % of the slots still found the link waiting). */
+	c.readers_max = c.ncpu <= 4 ? std::max(2, c.ncpu) : std::min(16, c.ncpu - 1);
 	c.readers_start = std::min(c.readers_max, std::max(2, std::min(6, c.ncpu * 3 / 8)));
 	const char *fixed = getenv("NVME_STROM_READERS");
 	if (fixed && *fixed)

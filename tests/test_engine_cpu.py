@@ -68,6 +68,8 @@ def test_engine_counts_the_cores_it_is_allowed_on(tmp_path, strom):
     assert "state 3 1572864 4 5 0" in out
     out = run_child(body, make_file(tmp_path, strom, 8), NVME_STROM_CPUS="0-63")
     assert "state 64 4194304 4 16 1" in out
+    out = run_child(body, make_file(tmp_path, strom, 8), NVME_STROM_CPUS="0-7")
+    assert "state 8 4194304 4 7 1" in out
 
 
 def test_pagecache_read_calibration(tmp_path, strom):
