@@ -302,8 +302,9 @@ def run_product(args):
         # not move with the staging geometry (all ranks at once, best of 3 passes)
         est = abi.engine_state(local_rank)
         source_total = calibrate.pagecache_aggregate(dev, path, first_page * 8192, shard_bytes, est["readers_max"], 3)
-        # beside the roofline: what a plain copy out of the page cache moves on this host (the same
-        # threads, 16 MB destinations that do not stay in cache).  A staged path cannot beat it.
+        # beside the roofline: what a plain copy out of the page cache moves on this host when its
+        # destination does not stay in cache (the same threads, 16 MB destinations of their own).  The
+        # staged path beats it while its ring stays cache-resident and falls to it when it does not.
         host_copy_total = calibrate.pagecache_aggregate(dev, path, first_page * 8192, shard_bytes, est["readers_max"], 2,
                                                         dest_bytes_per_thread=16 << 20)
 
@@ -509,7 +510,7 @@ def run_product(args):
                                   "page_cache_read_GBps": round(source_total, 2), "source_GBps": round(source_total, 2),
                                   "pipeline_source_GBps": round(pipeline_source_total, 2),
                                   "host_copy_GBps": round(host_copy_total, 2),
-                                  "frac_of_host_copy": round(e2e / host_copy_total, 4),
+                                  "e2e_over_host_copy": round(e2e / host_copy_total, 4),
                                   "bound": "h2d" if h2d_total <= source_total else "source",
                                   "peak": round(xfer_roof, 2), "frac": round(e2e / xfer_roof, 4),
                                   "frac_of_h2d": round(e2e / h2d_total, 4),
@@ -518,9 +519,10 @@ def run_product(args):
                                          "that was higher; page_cache_read: every rank's reader threads copy their shard out of the "
                                          "file's mapping into cache-resident scratch (strom_debug_pagecache_read: no ring, no device), "
                                          "all ranks at once, best of 3; pipeline_source (diagnosis): MEMCPY_SSD2GPU with the device "
-                                         "copy switched off; host_copy (the staged path's ceiling on this host, not part of the "
-                                         "roofline): the same threads copying into 16 MB destinations of their own that do not "
-                                         "stay in cache (strom_debug_host_copy)"},
+                                         "copy switched off; host_copy (context, not part of the roofline): the same threads "
+                                         "copying into 16 MB destinations of their own, which do not stay in cache "
+                                         "(strom_debug_host_copy) -- what a staged path falls to once its ring does not stay "
+                                         "cache-resident"},
             "engine": dict(abi.engine_state(local_rank), cpus_of_rank0=len(cpus_mine)),
         }
         if c5 is not None:

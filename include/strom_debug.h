@@ -64,9 +64,9 @@ int strom_debug_pagecache_read(int fdesc, uint64_t offset, uint64_t length, int 
 
 /* The same readers copying into a destination of dest_bytes_per_thread each that they walk round
  * and round (16 MB: it does not stay in a core's cache): the host's plain copy rate out of the page
- * cache.  A staged path -- file -> pinned buffer -> DMA -- cannot move more than this, and moves
- * less once the DMA engines read the buffers as well; reported beside the transfer roofline as
- * the staged path's ceiling on the box at hand. */
+ * cache, three DRAM passes per byte once a DMA engine reads the destination as well.  The staged
+ * path beats it for as long as its ring stays cache-resident (one or two GPUs: about twice this
+ * rate) and falls to it when it does not; reported beside the transfer roofline for context. */
 int strom_debug_host_copy(int fdesc, uint64_t offset, uint64_t length, int n_threads,
 						  uint64_t dest_bytes_per_thread, double *seconds);
 

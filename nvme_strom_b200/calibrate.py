@@ -55,7 +55,8 @@ def pagecache_aggregate(dev, path, offset, length, n_threads, passes=3, dest_byt
     readers per rank copying into cache-resident scratch (strom_debug_pagecache_read: no staging
     ring, no device).  All bytes over the slowest rank's time, best pass.  GB/s.
     dest_bytes_per_thread > 0: the host's plain copy rate instead (every reader walks a destination
-    of that size, which does not stay in cache) -- the ceiling of any staged path on this host."""
+    of that size, which does not stay in cache) -- what a staged path falls to when its ring does
+    not stay cache-resident."""
     world = dist.get_world_size() if dist.is_initialized() else 1
     fd = os.open(path, os.O_RDONLY)
     best = 0.0

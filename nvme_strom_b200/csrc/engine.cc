@@ -1183,7 +1183,8 @@ static int pagecache_read_rate(int fd, uint64_t offset, uint64_t length, int n_t
 		n_threads = cfg->readers_max;
 	const uint32_t sub = cfg->sub_bytes;
 	/* scratch_bytes > sub: every reader walks a destination of that size instead (a ring that does
-	 * NOT stay in its cache) -- the plain copy rate of the host, the ceiling of any staged path */
+	 * NOT stay in its cache) -- the plain copy rate of the host, which a staged path falls to when
+	 * its ring does not stay cache-resident */
 	const uint64_t scratch_sz = std::max<uint64_t>(sub, scratch_bytes / sub * sub);
 	std::atomic<uint64_t> cursor{0};
 	std::atomic<int> failed{0}, ready{0};
