@@ -1,5 +1,5 @@
 """One scan-kernel variant over one resident buffer, a few launches (ncu target).
-Usage: python tools/one_scan.py <variant> [MiB] [launches]"""
+Usage: python tools/one_scan.py <variant|default> [MiB] [launches]"""
 import ctypes as C
 import os
 import sys
@@ -14,7 +14,10 @@ from nvme_strom_b200.abi import lib
 variant = sys.argv[1]
 mib = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
-os.environ["NVME_STROM_SCAN_VARIANT"] = variant
+if variant in ("", "default"):            # the shipped library's own choice
+    os.environ.pop("NVME_STROM_SCAN_VARIANT", None)
+else:
+    os.environ["NVME_STROM_SCAN_VARIANT"] = variant
 base_pages = 8192
 host = np.empty(base_pages * 8192, dtype=np.uint8)
 for i in range(base_pages):
