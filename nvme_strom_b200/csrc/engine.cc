@@ -119,7 +119,8 @@ struct EngineConfig {
 	int      readers_start = 2, readers_max = 2;
 	bool     adaptive = true;
 	int      host_readers = 1;
-	int      copy_mode = 0;          /* 0 memcpy, 1 nta, 2 ntstore                              */
+	int      copy_mode = 0;          /* 0 memcpy, 1 nta, 2 ntstore, 3 stream (stores only)      */
+	int      host_copy_mode = 0;     /* the same for MEMCPY_SSD2RAM destinations                */
 	bool     write_combined = false;
 	int      spin_us = 0;
 	uint32_t zero_copy_piece = 64u << 20;   /* page-locked sources: one cudaMemcpyAsync per this much */
@@ -164,7 +165,10 @@ static EngineConfig load_config()
 	c.host_readers = env_int("NVME_STROM_HOST_READERS", std::min(c.ncpu, 8), 1, 256);
 	const char *m = getenv("NVME_STROM_COPY");
 	if (m && __builtin_cpu_supports("avx2"))
-		c.copy_mode = !strcmp(m, "nta") ? 1 : (!strcmp(m, "ntstore") ? 2 : 0);
+		c.copy_mode = !strcmp(m, "nta") ? 1 : (!strcmp(m, "ntstore") ? 2 : (!strcmp(m, "stream") ? 3 : 0));
+	const char *hm = getenv("NVME_STROM_HOST_COPY");
+	if (hm && __builtin_cpu_supports("avx2"))
+		c.host_copy_mode = !strcmp(hm, "nta") ? 1 : (!strcmp(hm, "ntstore") ? 2 : (!strcmp(hm, "stream") ? 3 : 0));
 	c.write_combined = env_int("NVME_STROM_WC", 0, 0, 1) != 0;
 	c.spin_us = env_int("NVME_STROM_SPIN_US", 0, 0, 100000);
 	c.zero_copy_piece = (uint32_t)env_int("NVME_STROM_ZC_PIECE_MB", 64, 1, 64) << 20;
@@ -223,17 +227,21 @@ static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
  *   nta      source lines are prefetched non-temporally ahead of the loads, so that page-cache
  *            bytes, which are read exactly once, do not push the staging ring out of the caches;
  *   ntstore  as nta, and the staging slot is written with streaming stores (the ring then lives in
- *            DRAM and its size stops mattering).
+ *            DRAM and its size stops mattering);
+ *   stream   streaming stores without the prefetch.
+ * NVME_STROM_HOST_COPY selects the same for MEMCPY_SSD2RAM, whose destination is the caller's DMA
+ * buffer (megabytes that no core reads again before a device does).
  * Both need AVX2 and 32-byte alignment (sub-pieces are 4 KB aligned on both sides); anything else
  * falls back to memcpy.
  */
-__attribute__((target("avx2"))) static void copy_lines_avx2(char *dst, const char *src, uint64_t n, bool stream_stores)
+__attribute__((target("avx2"))) static void copy_lines_avx2(char *dst, const char *src, uint64_t n, bool stream_stores,
+																	bool prefetch_nta)
 {
 	constexpr uint64_t kAhead = 1024;                     /* bytes of source prefetched ahead */
 	uint64_t i = 0;
 	for (; i + 64 <= n; i += 64)
 	{
-		if (i + kAhead < n)
+		if (prefetch_nta && i + kAhead < n)
 			_mm_prefetch(src + i + kAhead, _MM_HINT_NTA);
 		const __m256i a = _mm256_load_si256(reinterpret_cast<const __m256i *>(src + i));
 		const __m256i b = _mm256_load_si256(reinterpret_cast<const __m256i *>(src + i + 32));
@@ -314,7 +322,7 @@ static int copy_from_map(const SourceMap &m, char *dst, uint32_t len, uint64_t o
 	}
 	t_bus_recover = &recover;
 	if (n && mode && (((uintptr_t)dst | (uintptr_t)(m.base + off)) & 31) == 0)
-		copy_lines_avx2(dst, m.base + off, n, mode == 2);
+		copy_lines_avx2(dst, m.base + off, n, mode >= 2, mode == 1 || mode == 2);
 	else if (n)
 		memcpy(dst, m.base + off, n);
 	t_bus_recover = nullptr;
@@ -680,7 +688,7 @@ private:
 			{
 				const uint64_t t0 = rdtsc_now();
 				stats_dma_started();
-				int rc = fetch_piece(j, j.dst, 0);
+				int rc = fetch_piece(j, j.dst, cfg_->host_copy_mode);
 				stats_dma_finished(t0);
 				task_put(j.task, rc);
 			}

@@ -32,7 +32,8 @@ class SegmentPipeline:
     """N in-flight segments of ``segment_sz`` bytes landing in one mapped device buffer."""
 
     def __init__(self, device=0, segment_sz=32 << 20, nr_segments=6, verify=False, scan=True,
-                 scan_flags=abi.SCAN_DEFAULT, keep_results=False, via_ram=False, source_only=False):
+                 scan_flags=abi.SCAN_DEFAULT, keep_results=False, via_ram=False, source_only=False,
+                 ram_copy_chunk=4 << 20):
         """verify: also fetch every segment a second way (MEMCPY_SSD2RAM + H2D) and byte-compare
         the two copies on the GPU.  via_ram: do not use MEMCPY_SSD2GPU at all -- land in a host
         DMA buffer with MEMCPY_SSD2RAM and copy up from there (config C4's comparison arm)."""
@@ -49,6 +50,10 @@ class SegmentPipeline:
         self.scan = scan
         self.scan_flags = scan_flags
         self.keep_results = keep_results
+        # the host->device copy of a segment that came through MEMCPY_SSD2RAM goes up in pieces of
+        # this size: one 32 MB copy holds the H2D copy engine for 0.6 ms, during which the transfer
+        # engine's own 4 MB copies queue behind it, its 16 MB ring fills up and its readers stall
+        self.ram_copy_chunk = max(1 << 20, ram_copy_chunk)
         self.stream = torch.cuda.Stream(device=self.device)
         self.buffer = torch.empty(segment_sz * nr_segments, dtype=torch.uint8, device=self.device)
         self.totals = torch.zeros(abi.T_COUNT, dtype=torch.int64, device=self.device)
@@ -160,11 +165,9 @@ class SegmentPipeline:
                 slot.event.record(self.stream)
                 return
             if self.via_ram:
-                self.buffer[slot.offset:slot.offset + self.segment_sz].copy_(slot.ref_host, non_blocking=True)
-                self.h2d_bytes += self.segment_sz
+                self._copy_up(self.buffer[slot.offset:slot.offset + self.segment_sz], slot.ref_host)
             if self.verify:
-                slot.ref_dev.copy_(slot.ref_host, non_blocking=True)
-                self.h2d_bytes += self.segment_sz
+                self._copy_up(slot.ref_dev, slot.ref_host)
                 abi.check(lib.strom_scan_verify_pages_dev(
                     C.c_void_p(base), C.c_void_p(slot.ref_dev.data_ptr()), self.nr_chunks,
                     slot.first_page & 0xFFFFFFFF, self.scan_flags, slot.first_page * BLCKSZ, res,
@@ -174,6 +177,12 @@ class SegmentPipeline:
                     C.c_void_p(base), self.nr_chunks, slot.first_page & 0xFFFFFFFF, self.scan_flags,
                     res, C.c_void_p(self.totals.data_ptr()), st), "strom_scan_pages_dev")
             slot.event.record(self.stream)
+
+    def _copy_up(self, dst, src):
+        for off in range(0, self.segment_sz, self.ram_copy_chunk):
+            end = min(off + self.ram_copy_chunk, self.segment_sz)
+            dst[off:end].copy_(src[off:end], non_blocking=True)
+        self.h2d_bytes += self.segment_sz
 
     # -- whole range ------------------------------------------------------------
     def run(self, path, first_segment=0, n_segments=None, relseg_sz=0):
