@@ -166,9 +166,13 @@ static EngineConfig load_config()
 	const char *m = getenv("NVME_STROM_COPY");
 	if (m && __builtin_cpu_supports("avx2"))
 		c.copy_mode = !strcmp(m, "nta") ? 1 : (!strcmp(m, "ntstore") ? 2 : (!strcmp(m, "stream") ? 3 : 0));
+	/* MEMCPY_SSD2RAM lands megabytes in the caller's DMA buffer that no core touches again before a
+	 * device (or, much later, the caller) reads them: long pieces are written with streaming stores,
+	 * which spares the read-for-ownership pass (load + scan + byte-compare, where this leg shares the
+	 * memory system with the GPU engine: 17-18.6 -> 21.5-22 GB/s, profiles/r02_verify_bench.txt) */
 	const char *hm = getenv("NVME_STROM_HOST_COPY");
-	if (hm && __builtin_cpu_supports("avx2"))
-		c.host_copy_mode = !strcmp(hm, "nta") ? 1 : (!strcmp(hm, "ntstore") ? 2 : (!strcmp(hm, "stream") ? 3 : 0));
+	if (__builtin_cpu_supports("avx2"))
+		c.host_copy_mode = !hm ? 3 : (!strcmp(hm, "nta") ? 1 : (!strcmp(hm, "ntstore") ? 2 : (!strcmp(hm, "stream") ? 3 : 0)));
 	c.write_combined = env_int("NVME_STROM_WC", 0, 0, 1) != 0;
 	c.spin_us = env_int("NVME_STROM_SPIN_US", 0, 0, 100000);
 	c.zero_copy_piece = (uint32_t)env_int("NVME_STROM_ZC_PIECE_MB", 64, 1, 64) << 20;
@@ -230,7 +234,8 @@ static int read_fully(int fd, char *buf, uint32_t len, uint64_t off)
  *            DRAM and its size stops mattering);
  *   stream   streaming stores without the prefetch.
  * NVME_STROM_HOST_COPY selects the same for MEMCPY_SSD2RAM, whose destination is the caller's DMA
- * buffer (megabytes that no core reads again before a device does).
+ * buffer (megabytes that no core reads again before a device does): default "stream" for pieces of
+ * 1 MB and more, "memcpy" switches it off.
  * Both need AVX2 and 32-byte alignment (sub-pieces are 4 KB aligned on both sides); anything else
  * falls back to memcpy.
  */
@@ -688,7 +693,7 @@ private:
 			{
 				const uint64_t t0 = rdtsc_now();
 				stats_dma_started();
-				int rc = fetch_piece(j, j.dst, cfg_->host_copy_mode);
+				int rc = fetch_piece(j, j.dst, j.length >= (1u << 20) ? cfg_->host_copy_mode : 0);
 				stats_dma_finished(t0);
 				task_put(j.task, rc);
 			}

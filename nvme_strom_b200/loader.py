@@ -33,7 +33,7 @@ class SegmentPipeline:
 
     def __init__(self, device=0, segment_sz=32 << 20, nr_segments=6, verify=False, scan=True,
                  scan_flags=abi.SCAN_DEFAULT, keep_results=False, via_ram=False, source_only=False,
-                 ram_copy_chunk=4 << 20):
+                 ram_copy_chunk=None):
         """verify: also fetch every segment a second way (MEMCPY_SSD2RAM + H2D) and byte-compare
         the two copies on the GPU.  via_ram: do not use MEMCPY_SSD2GPU at all -- land in a host
         DMA buffer with MEMCPY_SSD2RAM and copy up from there (config C4's comparison arm)."""
@@ -50,10 +50,10 @@ class SegmentPipeline:
         self.scan = scan
         self.scan_flags = scan_flags
         self.keep_results = keep_results
-        # the host->device copy of a segment that came through MEMCPY_SSD2RAM goes up in pieces of
-        # this size: one 32 MB copy holds the H2D copy engine for 0.6 ms, during which the transfer
-        # engine's own 4 MB copies queue behind it, its 16 MB ring fills up and its readers stall
-        self.ram_copy_chunk = max(1 << 20, ram_copy_chunk)
+        # a segment that came through MEMCPY_SSD2RAM goes up in one copy; cutting it into pieces that
+        # interleave with the transfer engine's 4 MB copies was measured and changes nothing
+        # (profiles/r02_verify_bench.txt: 32 / 8 / 4 / 2 MB pieces 19.1-20.1 GB/s, 1 MB 17.7)
+        self.ram_copy_chunk = segment_sz if not ram_copy_chunk else max(1 << 20, ram_copy_chunk)
         self.stream = torch.cuda.Stream(device=self.device)
         self.buffer = torch.empty(segment_sz * nr_segments, dtype=torch.uint8, device=self.device)
         self.totals = torch.zeros(abi.T_COUNT, dtype=torch.int64, device=self.device)
