@@ -263,7 +263,8 @@ print("split", a.nr_ram2gpu, a.nr_ssd2gpu)
 @pytest.mark.parametrize("env", [{"NVME_STROM_IO": "direct"}, {"NVME_STROM_SRC": "pread"}, {"NVME_STROM_FIEMAP": "0"},
                                  {"NVME_STROM_READERS": "1", "NVME_STROM_SLOT_KB": "128", "NVME_STROM_SLOTS": "2"},
                                  {"NVME_STROM_WC": "1", "NVME_STROM_SUB_KB": "64", "NVME_STROM_SLOTS": "3"},
-                                 {"NVME_STROM_READERS": "12", "NVME_STROM_SLOT_KB": "512", "NVME_STROM_SPIN_US": "50"}])
+                                 {"NVME_STROM_READERS": "12", "NVME_STROM_SLOT_KB": "512", "NVME_STROM_SPIN_US": "50"},
+                                 {"NVME_STROM_COPY": "stream"}, {"NVME_STROM_COPY": "ntstore", "NVME_STROM_CPUS": "0-3"}])
 def test_io_modes_land_the_same_bytes(heapfile, env):
     """O_DIRECT, pread, no FIEMAP, a single reader with tiny slots: same bytes, same counters.
     The switches are read once per process, so each mode runs in a child."""
@@ -290,3 +291,29 @@ print("ok", a.nr_dma_submit)
     r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), capture_output=True, text=True,
                        timeout=300)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_engine_reports_what_it_decided(heapfile, filedata):
+    """the self-adjusting engine after a run of loads: it counts the cores this process may use, keeps
+    its reader count inside [2, readers], and accounts for every staged slot"""
+    import torch
+    from gpu_util import map_gpu, ssd2gpu, unmap_gpu, wait
+    from nvme_strom_b200 import abi
+    n = min(8192, filedata.size // 8192)
+    buf = torch.zeros(n * 8192, dtype=torch.uint8, device="cuda")
+    m = map_gpu(buf)
+    fd = os.open(heapfile, os.O_RDONLY)
+    before = abi.engine_state(0)
+    for _ in range(6):
+        a, keep = ssd2gpu(m.handle, 0, fd, list(range(n)))
+        assert wait(a.dma_task_id) == 0
+    os.close(fd)
+    st = abi.engine_state(0)
+    unmap_gpu(m.handle)
+    assert (buf.cpu().numpy() == filedata[:n * 8192]).all()
+    assert st["allowed_cpus"] == len(os.sched_getaffinity(0))
+    assert st["readers"] == st["readers_max"] >= 2 and 2 <= st["readers_active"] <= st["readers"]
+    assert st["slots_staged"] - before["slots_staged"] >= 6 * n * 8192 // st["slot_bytes"]
+    assert st["slots_starved"] <= st["slots_staged"]
+    if os.environ.get("NVME_STROM_READERS"):
+        assert not st["adaptive"] and st["grown"] == st["shrunk"] == 0
