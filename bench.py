@@ -41,6 +41,29 @@ SEED = 0x5EED0001
 METRIC = "page_checksum_scan_GBps"
 
 
+_OUT_FD = None
+
+
+def claim_stdout():
+    """stdout is for the ONE JSON line.  Libraries write banners to file descriptor 1 behind Python's
+    back (NCCL's version line does, whatever NCCL_DEBUG_FILE says, on some boxes), so descriptor 1 is
+    pointed at stderr for the whole run and the line goes out through a private copy of the original."""
+    global _OUT_FD
+    if _OUT_FD is None:
+        sys.stdout.flush()
+        _OUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _OUT_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_OUT_FD, line)
+
+
 def env_rank():
     return (int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")),
             int(os.environ.get("WORLD_SIZE", "1")))
@@ -172,7 +195,7 @@ def run_reference(args):
                              "ms_per_step_with_setup": round(dt_wall * 1e3, 3)},
             "e2e": {"value": round(val, 3), "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -558,7 +581,7 @@ def run_product(args):
         finally:
             os.unlink(path)
     if rank == 0:
-        print(json.dumps(result))
+        emit(result)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -574,6 +597,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-c5", action="store_true", help="skip the untimed mixed-validity (C5) exact-count leg")
     args = ap.parse_args()
+    claim_stdout()
     if args.impl == "reference":
         return run_reference(args)
     return run_product(args)

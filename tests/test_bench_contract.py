@@ -46,7 +46,9 @@ def test_reference_arm_maps_no_product_library():
             "assert 'libnvme_strom' not in maps, [l for l in maps.splitlines() if 'libnvme_strom' in l]\n"
             "print('CLEAN')")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0 and "CLEAN" in r.stdout, r.stdout[-1500:] + r.stderr[-3000:]
+    # bench.py points descriptor 1 at stderr for everything but its one JSON line
+    assert r.returncode == 0 and "CLEAN" in r.stdout + r.stderr, r.stdout[-1500:] + r.stderr[-3000:]
+    assert len([l for l in r.stdout.splitlines() if l.strip()]) == 1
 
 
 def test_reference_arm_other_ranks_stay_silent():
