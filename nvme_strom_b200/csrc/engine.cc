@@ -11,7 +11,7 @@
  *
  *   - one engine per (device, context): reader threads, one ring of pinned
  *     slots, one CUDA stream, one event per slot;
- *   - a piece is one slot.  Readers take 1 MB sub-pieces of the slot being
+ *   - a piece is one slot.  Readers take sub-pieces (256 KB, or half a slot) of the slot being
  *     filled; whoever finishes the last one queues the copy of the whole slot
  *     and everybody moves on to the next slot of the ring while it is in
  *     flight; a slot's event is waited for only when the ring comes round to
@@ -46,7 +46,7 @@
  * adjusting between 2 and all allowed cores but one, at most 16),
  * NVME_STROM_SLOT_KB (staging slot; unset: 4096, or 512 per allowed core below
  * 8 cores), NVME_STROM_SLOTS (ring length, default 4), NVME_STROM_SUB_KB (what
- * one reader copies at a time, default 1024 or half a slot), NVME_STROM_SPIN_US (yield-spin
+ * one reader copies at a time; unset: 256, or half a slot where slots are 2 MB or less), NVME_STROM_SPIN_US (yield-spin
  * before sleeping on a busy slot, default 0: no measurable gain),
  * NVME_STROM_HOST_READERS (SSD2RAM threads, default min(8, cores)),
  * NVME_STROM_COPY (memcpy | nta | ntstore).  All are read when the first engine
@@ -146,11 +146,13 @@ static EngineConfig load_config()
 	const int slot_kb_dflt = c.ncpu >= 8 ? 4096 : std::max(1024, c.ncpu * 512);
 	c.slot_bytes = (uint32_t)env_int("NVME_STROM_SLOT_KB", slot_kb_dflt, 128, 65536) << 10;
 	c.slots = env_int("NVME_STROM_SLOTS", 4, 2, 64);
-	/* what one reader copies at a time: 1 MB, at most half a slot.  With one GPU anything from 128 KB
-	 * to 1 MB gives the same rate (a whole 4 MB slot per reader loses 8 %); with eight GPUs on one
-	 * host, where the memory system is the limit, 1 MB runs on 2 MB slots move 87-96 GB/s where
-	 * 256 KB moved 72-75 and whole slots 74 (profiles/r02_ring_n8_subpieces.txt) */
-	const int sub_kb_dflt = (int)std::max<uint32_t>(64, std::min<uint32_t>(1024, (c.slot_bytes >> 10) / 2));
+	/* what one reader copies at a time.  Where an engine has cores to spare the link is the limit and
+	 * what counts is how soon a slot is complete: 256 KB, so that every reader works on the slot being
+	 * filled (two GPUs, 12 cores each: 102 GB/s; with 1 MB pieces 75).  Where it has few (one rank of
+	 * eight on a 32-core host, 2 MB slots) the host's memory system is the limit and long runs per
+	 * reader win: half a slot, 1 MB, moves 87-98 GB/s where 256 KB moved 72-75 and whole slots 74
+	 * (profiles/r02_ring_n8_subpieces.txt).  One GPU alone does not care (128 KB .. 1 MB: 50-52). */
+	const int sub_kb_dflt = c.slot_bytes <= (2u << 20) ? (int)std::max<uint32_t>(64, (c.slot_bytes >> 10) / 2) : 256;
 	c.sub_bytes = (uint32_t)env_int("NVME_STROM_SUB_KB", sub_kb_dflt, 64, 65536) << 10;
 	/* readers: a lone GPU is link-bound from about 6 on, so that is where an engine starts; how many
 	 * of its threads take part after that is decided by trial (Engine::account_slot), up to all
@@ -717,7 +719,7 @@ private:
 	 * readers there are, so the staged bytes are still in cache when the slot is
 	 * written again, and eight engines on one host do not evict each other (profiles/
 	 * r01_slot_sweep.txt: with private slots the footprint was readers x 2 x slot, and the box's
-	 * aggregate rate fell as it grew).  A piece is one slot; readers take 1 MB sub-pieces of the
+	 * aggregate rate fell as it grew).  A piece is one slot; readers take sub-pieces of the
 	 * slot being filled, whoever finishes the last one sends the whole slot up with a single
 	 * cudaMemcpyAsync on the engine's one stream, so the copy engine sees long back-to-back copies
 	 * whatever the reader count.  Slots are used in ring order; a slot is waited for (its event)
