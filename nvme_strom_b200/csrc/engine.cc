@@ -801,9 +801,8 @@ private:
 	 *   - two or more starved slots in a window (3 %): one more reader, kept only if the next
 	 *     window moved at least 3 % more bytes per second; otherwise taken back, and no further
 	 *     growth is tried for a while that doubles with every failed trial;
-	 *   - every eight windows, while less than a quarter of the slots are starved: one reader
-	 *     fewer, kept unless the next window lost more than 2 %; a failed trial again doubles the
-	 *     wait before the next.
+	 *   - eight windows in a row without a starved slot: one reader fewer, kept unless the next
+	 *     window lost more than 2 %; a failed trial again doubles the wait before the next.
 	 * Windows that contain a pause (the caller had nothing queued) say nothing and are skipped.
 	 */
 	static double now_s()
@@ -847,12 +846,7 @@ private:
 				else { n_grown_++; park_cv_.notify_all(); shrink_hold_ = shrink_hold_next_; shrink_hold_next_ = std::min<uint32_t>(shrink_hold_next_ * 2, 4096); }
 			}
 			else if (trial_ > 0)
-			{
-				grow_hold_next_ = 8;                  /* growth paid off: keep probing readily ... */
-				grow_hold_ = 2;                       /* ... after a breath                      */
-			}
-			else
-				shrink_hold_next_ = 32;               /* one fewer did no harm                   */
+				grow_hold_next_ = 8;                  /* growth paid off: keep probing readily */
 			trial_ = 0;
 			calm_ = 0;
 		}
@@ -860,21 +854,7 @@ private:
 		{
 			if (grow_hold_ > 0) grow_hold_--;
 			if (shrink_hold_ > 0) shrink_hold_--;
-			calm_++;                                  /* windows since the last change */
-			/* Letting one go is tried every eight windows as long as less than a quarter of the
-			 * slots are starved, not only when none is: near the link-bound point a few per cent
-			 * stay starved whatever the count, growth trials that pass on noise add up (two GPUs,
-			 * 12 cores each: 10 of 11 readers and 94 GB/s where 7 gave 102), and only a trial the
-			 * other way takes them back. */
-			if (calm_ >= 8 && shrink_hold_ == 0 && active_ > 2 && win_starved_ * 4 < win_issued_)
-			{
-				trial_base_ = rate;
-				trial_ = -1;
-				active_--;
-				n_shrunk_++;
-				calm_ = 0;
-			}
-			else if (win_starved_ >= 2 && active_ < max && grow_hold_ == 0)
+			if (win_starved_ >= 2 && active_ < max && grow_hold_ == 0)
 			{
 				trial_base_ = rate;
 				trial_ = +1;
@@ -883,6 +863,19 @@ private:
 				park_cv_.notify_all();
 				calm_ = 0;
 			}
+			else if (win_starved_ == 0 && active_ > 2)
+			{
+				if (++calm_ >= 8 && shrink_hold_ == 0)
+				{
+					trial_base_ = rate;
+					trial_ = -1;
+					active_--;
+					n_shrunk_++;
+					calm_ = 0;
+				}
+			}
+			else
+				calm_ = 0;
 		}
 		win_issued_ = win_starved_ = 0;
 		win_bytes_ = 0;
