@@ -11,8 +11,8 @@
  *
  *   - one engine per (device, context): reader threads, one ring of pinned
  *     slots, one CUDA stream, one event per slot;
- *   - a piece is one slot.  Readers take sub-pieces (256 KB, or half a slot) of the slot being
- *     filled; whoever finishes the last one queues the copy of the whole slot
+ *   - a piece is one slot.  Readers take sub-pieces (256 KB, or half a slot)
+ *     of the slot being filled; whoever finishes the last one queues the copy of the whole slot
  *     and everybody moves on to the next slot of the ring while it is in
  *     flight; a slot's event is waited for only when the ring comes round to
  *     it, or when there is nothing else to do;
@@ -22,9 +22,11 @@
  *   - the number of readers that take part follows the copy stream: a slot
  *     queued behind a copy that had already finished, with more pieces
  *     waiting, means the source side starved the link, and another reader is
- *     let in; a long run without a single such slot lets one go again.  The
- *     rest stay parked and cost nothing (profiles/r02_*: past the link-bound
- *     point extra readers only add lock and wake-up traffic);
+ *     let in on trial -- kept only if the next window of slots moved more
+ *     bytes per second; a long run without a single starved slot lets one go
+ *     on the same terms.  The rest stay parked and cost nothing (profiles/
+ *     r02_*: past the link-bound point extra readers only add lock and
+ *     wake-up traffic);
  *   - page-locked sources (nvme_strom_pin_file) skip the staging: the copy
  *     engine reads the page cache itself and the slot lends only its event;
  *   - completion is a host-side refcount drop (task_put): MEMCPY_WAIT sleeps
@@ -46,10 +48,11 @@
  * adjusting between 2 and all allowed cores but one, at most 16),
  * NVME_STROM_SLOT_KB (staging slot; unset: 4096, or 512 per allowed core below
  * 8 cores), NVME_STROM_SLOTS (ring length, default 4), NVME_STROM_SUB_KB (what
- * one reader copies at a time; unset: 256, or half a slot where slots are 2 MB or less), NVME_STROM_SPIN_US (yield-spin
- * before sleeping on a busy slot, default 0: no measurable gain),
- * NVME_STROM_HOST_READERS (SSD2RAM threads, default min(8, cores)),
- * NVME_STROM_COPY (memcpy | nta | ntstore).  All are read when the first engine
+ * one reader copies at a time; unset: 256, or half a slot where slots are 2 MB
+ * or less), NVME_STROM_SPIN_US (yield-spin before sleeping on a busy slot,
+ * default 0: no measurable gain), NVME_STROM_HOST_READERS (SSD2RAM threads,
+ * default min(8, cores)), NVME_STROM_COPY (memcpy | nta | ntstore | stream),
+ * NVME_STROM_HOST_COPY (stream | memcpy).  All are read when the first engine
  * is made (strom_debug_reconfigure() re-reads them: tuning tools only).
  */
 #include "strom_internal.h"

@@ -63,3 +63,31 @@ def test_proc_entry_banner_through_the_shim(tmp_path):
     """cat /proc/nvme-strom prints the version banner (kmod/nvme_strom.c:2036-2061)"""
     r = run(["cat", "/proc/nvme-strom"], timeout=30)
     assert r.returncode == 0 and r.stdout.startswith("version: ")
+
+
+def test_shim_refuses_a_descriptor_it_cannot_track(tmp_path):
+    """the shim remembers sessions per descriptor below 4096; past that it fails the open like a full
+    descriptor table (EMFILE) instead of handing back a descriptor whose ioctls would end in ENOTTY"""
+    import subprocess
+    import sys
+    from nvme_strom_b200._lib import PRELOAD_PATH
+    code = r'''
+import errno, os, resource
+soft, hard = resource.getrlimit(resource.RLIMIT_NOFILE)
+want = 6000
+if hard != resource.RLIM_INFINITY and hard < want:
+    print("SKIP"); raise SystemExit(0)
+resource.setrlimit(resource.RLIMIT_NOFILE, (want, hard))
+fd = os.open("/proc/nvme-strom", os.O_RDONLY)          # low descriptor: tracked
+os.close(fd)
+keep = [os.dup(0) for _ in range(4200)]
+try:
+    os.open("/proc/nvme-strom", os.O_RDONLY)
+    print("OPENED")
+except OSError as e:
+    print("ERRNO", e.errno == errno.EMFILE)
+'''
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, LD_PRELOAD=PRELOAD_PATH),
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "SKIP" in r.stdout or "ERRNO True" in r.stdout, r.stdout + r.stderr
