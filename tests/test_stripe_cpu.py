@@ -138,8 +138,12 @@ def test_striped_plans_match_the_oracle_planner(ora, strom, to_gpu):
             extents.append((lc // 4096, stripe // 4096, (member << 36) + off // 512))
         dest_len = n * chunk_sz + (1 << 20)
         seg = 0 if to_gpu else 4 << 20
-        got = run_product_striped(strom, to_gpu, ids, chunk_sz, 0, sizes, stripe, 0, dest_len, seg)
-        want = run_oracle(ora, to_gpu, ids, chunk_sz, 0, total, None, extents, 0, dest_len, seg)
+        # every fourth trial addresses the set as a relation of relseg-chunk segments (ids wrap, :1526-1527)
+        relseg = max(1, n_file_chunks // 2) if trial % 4 == 3 else 0
+        if relseg:
+            ids = [i + relseg * int(rng.integers(0, 3)) for i in (x % relseg for x in ids)]
+        got = run_product_striped(strom, to_gpu, ids, chunk_sz, relseg, sizes, stripe, 0, dest_len, seg)
+        want = run_oracle(ora, to_gpu, ids, chunk_sz, relseg, total, None, extents, 0, dest_len, seg)
         assert got[0] == want[0] == 0
         assert got[1] == want[1], (trial, sizes, stripe, chunk_sz, ids[:8], got[1], want[1])
         assert got[2] == want[2]
